@@ -1,0 +1,154 @@
+/* peasoup_b200.h -- C ABI of libpeasoup_b200.so
+ *
+ * Drop-in boundary for the per-DM acceleration-search hot path of peasoup.  Every entry
+ * point replaces one free function of the reference's kernel API
+ * (/root/reference/include/kernels/kernels.h) or one cuFFT call site
+ * (include/transforms/ffter.hpp); the citation beside each declaration names it.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; all `d_*` pointers are device pointers on the current
+ *    CUDA device, `h_*` are host pointers;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream).  Unlike the
+ *    reference (which ends every wrapper in cudaDeviceSynchronize, utils/exceptions.hpp:64-74)
+ *    calls are asynchronous unless they return a value to the host;
+ *  - return value: 0 on success, a negative PS_E* code on failure; ps_last_error() returns a
+ *    thread-local message with the same prefixes the reference's ErrorChecker uses
+ *    ("CUDA failed with error: ...").  The C++ wrappers in include/peasoup_b200/ rethrow it
+ *    as std::runtime_error like the reference does;
+ *  - there is no CPU fallback: without a CUDA device every compute call fails with PS_ECUDA.
+ */
+#ifndef PEASOUP_B200_H
+#define PEASOUP_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PS_OK 0
+#define PS_ECUDA (-1)   /* CUDA runtime error (message in ps_last_error) */
+#define PS_EINVAL (-2)  /* bad argument / unsupported size */
+#define PS_EOVERFLOW (-3) /* more peaks than the workspace holds */
+
+typedef struct { float re, im; } ps_complex; /* layout of cufftComplex / float2 */
+
+const char* ps_last_error(void);
+int ps_version(void);
+
+/* ---------------- staged kernel API (one function per reference function) ------------- */
+
+/* device_resampleII, kernels.h:126 / kernels.cu:314-317,335-362.
+ * d_out[i] = d_in[rn(i + i*af*(i-n))], af = double(a*tsamp)/(2c); bit-exact index map. */
+int ps_resampleII(const float* d_in, float* d_out, size_t n, float a, float tsamp, void* stream);
+/* device_resample, kernels.h:118 / kernels.cu:308-311,320-332,364-379 (v1 index map). */
+int ps_resample(const float* d_in, float* d_out, size_t n, float a, float tsamp, void* stream);
+/* Index maps only (uint32 read index for every output sample); test/diagnostic aid for the
+ * bit-exact parity gate.  which = 1 -> resample (v1), 2 -> resampleII. */
+int ps_resample_index_map(uint32_t* d_idx, size_t n, float a, float tsamp, int which, void* stream);
+
+/* device_form_power_series, kernels.h:111 / kernels.cu:215-252,287-304.
+ * way = 0: |X| (z*rsqrtf(z)); way = 1: interbinned amplitude. */
+int ps_form_power_series(const ps_complex* d_in, float* d_out, size_t nbins, int way, void* stream);
+
+/* device_normalise, kernels.h:144 / kernels.cu:469-494: d[i] = (d[i]-mean)/sigma. */
+int ps_normalise(float* d_powers, float mean, float sigma, unsigned nbins, void* stream);
+
+/* device_harmonic_sum, kernels.h:104 / kernels.cu:33-99,199-208.
+ * h_out_ptrs: HOST array of nfolds DEVICE pointers (the reference re-uploads a device table
+ * per call, harmonicfolder.hpp:29-33; here the pointers travel as kernel arguments). nfolds<=5. */
+int ps_harmonic_sum(const float* d_in, float* const* h_out_ptrs, size_t nbins, unsigned nfolds,
+                    void* stream);
+
+/* device_find_peaks, kernels.h:134 / kernels.cu:384-416.  Stream-compacts (idx,value) with
+ * value > thresh for idx in [start,n) in ascending idx order into the host arrays (capacity
+ * max_out each).  The Thrust vectors + cached_allocator of the reference become an opaque
+ * workspace.  Returns the count (>=0) or a negative error; synchronises the stream. */
+typedef struct ps_peak_workspace ps_peak_workspace;
+int ps_peak_workspace_create(size_t max_peaks, ps_peak_workspace** out);
+void ps_peak_workspace_destroy(ps_peak_workspace* ws);
+int ps_find_peaks(int n, int start, const float* d_dat, float thresh, int* h_idx, float* h_snr,
+                  size_t max_out, ps_peak_workspace* ws, void* stream);
+
+/* median_scrunch5 / linear_stretch, kernels.h:252,256 / kernels.cu:875-1011. */
+int ps_median_scrunch5(const float* d_in, size_t count, float* d_out, void* stream);
+int ps_linear_stretch(const float* d_in, size_t in_count, float* d_out, size_t out_count,
+                      void* stream);
+/* Dereddener::calculate_median, dereddener.hpp:41-62, as ONE call: three scrunch levels and
+ * the spliced 5/25/125 stretch evaluated on the fly.  d_work: >= nbins/5+nbins/25+nbins/125+3
+ * floats. */
+int ps_running_median(const float* d_pspec, unsigned nbins, double bin_width, float boundary_5_freq,
+                      float boundary_25_freq, float* d_median, float* d_work, void* stream);
+/* device_divide_c_by_f, kernels.h:262 / kernels.cu:1013-1034. */
+int ps_divide_c_by_f(ps_complex* d_c, const float* d_f, unsigned nbins, void* stream);
+/* device_zap_birdies, kernels.h:268 / kernels.cu:1036-1069 (width is a half-width). */
+int ps_zap_birdies(ps_complex* d_c, const float* d_birdies, const float* d_widths, float bin_width,
+                   unsigned nbirdies, unsigned nbins, void* stream);
+
+/* GPU_rms / GPU_mean / GPU_fill, kernels.h:279-292 / kernels.cu:426-463.  Synchronous. */
+int ps_rms(const float* d, int nsamps, int min_bin, float* out);
+int ps_mean(const float* d, int nsamps, int min_bin, float* out);
+int ps_fill(float* d_start, float* d_end, float value, void* stream);
+/* device_conversion<unsigned char,float>, kernels.h:318 / kernels.cu:1144-1170. */
+int ps_convert_u8_f32(const unsigned char* d_in, float* d_out, unsigned n, void* stream);
+
+/* ---------------- FFT (replaces cuFFT, ffter.hpp:46-78) ------------------------------- */
+typedef struct ps_fft_plan ps_fft_plan;
+/* cufftPlan1d(&plan, n, CUFFT_R2C/C2R, 1): n a power of two, 2^17 <= n <= 2^25. */
+int ps_fft_plan_create(unsigned n, ps_fft_plan** out);
+void ps_fft_plan_destroy(ps_fft_plan* plan);
+/* cufftExecR2C: n floats -> n/2+1 complex, unnormalised. */
+int ps_fft_r2c(ps_fft_plan* plan, const float* d_in, ps_complex* d_out, void* stream);
+/* cufftExecC2R: n/2+1 complex -> n floats, unnormalised (x n). */
+int ps_fft_c2r(ps_fft_plan* plan, const ps_complex* d_in, float* d_out, void* stream);
+
+/* ---------------- fused search path (Worker::start, pipeline_multi.cu:100-252) -------- */
+typedef struct {
+  unsigned size;        /* transform length, --fft_size / prev_power_of_two (pipeline_multi.cu:326-331) */
+  unsigned nsamps;      /* samples per dedispersed trial (may be < or > size: padding path :112-114) */
+  float tsamp;          /* seconds, float as in timeseries.hpp:54 */
+  int nharmonics;       /* number of folds 0..5 (--nharmonics) */
+  float min_snr;        /* --min_snr */
+  float min_freq;       /* --min_freq */
+  float max_freq;       /* --max_freq */
+  float boundary_5_freq;  /* 0.05 (the reference never forwards the CLI value, dereddener.hpp:41-43) */
+  float boundary_25_freq; /* 0.5 */
+  unsigned max_peaks;   /* capacity of the per-DM raw peak list (0 -> default 1<<20) */
+} ps_search_params;
+
+/* One record per above-threshold bin, before clustering (peakfinder.hpp:27-56 runs on host). */
+typedef struct {
+  int32_t acc_idx;  /* index into the acceleration list of this DM trial */
+  int32_t nh;       /* 0 = fundamental spectrum, k = k-th fold */
+  int32_t bin;      /* spectrum bin */
+  float snr;        /* normalised amplitude */
+} ps_raw_peak;
+
+typedef struct ps_search ps_search;
+int ps_search_create(const ps_search_params* p, ps_search** out);
+void ps_search_destroy(ps_search* s);
+/* zaplist (birdiezapper.hpp:34-57): nbirdies host floats each; copies to the device. */
+int ps_search_set_zaplist(ps_search* s, const float* h_freqs, const float* h_widths, unsigned n);
+/* Per-DM whitening chain, pipeline_multi.cu:157-204: u8 trial (DEVICE pointer, nsamps bytes)
+ * -> whitened time series kept inside the handle, plus mean/std of the whitened interbinned
+ * spectrum (device-resident; also copied to *h_mean,*h_std if non-NULL, which synchronises). */
+int ps_search_whiten(ps_search* s, const unsigned char* d_trial, float* h_mean, float* h_std,
+                     void* stream);
+/* Acceleration loop, pipeline_multi.cu:209-239 up to device_find_peaks: for each acceleration
+ * resample -> R2C -> interbin -> normalise -> harmonic sums -> threshold.  Appends raw peaks to
+ * the handle's device list.  Asynchronous. */
+int ps_search_accel_batch(ps_search* s, const float* h_acc, int n_acc, int acc_idx0, void* stream);
+/* Reset / fetch the device peak list (fetch synchronises; records are sorted by
+ * (acc_idx, nh, bin), i.e. the order the reference's per-spectrum copy_if calls produce). */
+int ps_search_reset_peaks(ps_search* s, void* stream);
+long ps_search_fetch_peaks(ps_search* s, ps_raw_peak* h_out, size_t max_out, void* stream);
+/* Diagnostics for stage-by-stage parity tests: device pointers owned by the handle. */
+const float* ps_search_whitened_series(ps_search* s);   /* size floats */
+const float* ps_search_last_spectrum(ps_search* s);     /* size/2+1 floats (last accel trial) */
+/* kernel launch counter (all ps_* kernels launched by this process; for bench.py) */
+unsigned long long ps_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PEASOUP_B200_H */

@@ -1,0 +1,236 @@
+// fft_core.cuh -- CTA-level complex FFT building blocks (sm_100a; also compiles as plain
+// C++ so that tests/cpu_emul can execute the exact same index math on the host).
+//
+// Replaces the cuFFT plans of the reference (include/transforms/ffter.hpp:46-78) with a
+// hand-written two-pass ("four-step") transform.  One CTA of 512 threads performs F
+// independent length-n FFTs at a time, n = 16*16*R3 (R3 in {1,2,4,8,16} => n = 256..4096),
+// F = 32/R3, so that F*R3 = 32 and every shared-memory access of a warp is 32 consecutive
+// words (bank-conflict free, see DESIGN.md "FFT shared-memory layout").
+//
+// Each thread owns 16 complex values.  Decimation in frequency with digits
+//   j = a*(n/16) + b*R3 + c         (a,b in [0,16), c in [0,R3))
+//   k = ka + 16*kb + 256*kc
+// phase A: radix-16 over a, twiddle W_n^(ka*(b*R3+c))        -> exchange E1
+// phase B: radix-16 over b, twiddle W_(16*R3)^(kb*c)          -> exchange E2
+// phase C: radix-R3 over c                                    -> Storer(f, k, value)
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define PS_HD __host__ __device__ __forceinline__
+#else
+#define PS_HD inline
+#endif
+
+namespace psfft {
+
+struct alignas(8) cf {
+  float x, y;
+};
+
+PS_HD cf mk(float x, float y) {
+  cf r;
+  r.x = x;
+  r.y = y;
+  return r;
+}
+// read-only (non-coherent) load of a table entry
+PS_HD cf ldg_cf(const cf* p) {
+#if defined(__CUDA_ARCH__)
+  float2 v = __ldg(reinterpret_cast<const float2*>(p));
+  return mk(v.x, v.y);
+#else
+  return *p;
+#endif
+}
+PS_HD cf cadd(cf a, cf b) { return mk(a.x + b.x, a.y + b.y); }
+PS_HD cf csub(cf a, cf b) { return mk(a.x - b.x, a.y - b.y); }
+PS_HD cf cmul(cf a, cf b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+PS_HD cf cconj(cf a) { return mk(a.x, -a.y); }
+// multiply by -i (forward transform) or +i (inverse transform)
+template <bool INV>
+PS_HD cf rot(cf a) {
+  return INV ? mk(-a.y, a.x) : mk(a.y, -a.x);
+}
+// twiddle tables hold forward roots exp(-2*pi*i*q/n); inverse transforms conjugate them
+template <bool INV>
+PS_HD cf dirw(cf w) {
+  return INV ? mk(w.x, -w.y) : w;
+}
+
+template <bool INV>
+PS_HD void dft2(cf& a, cf& b) {
+  cf t = a;
+  a = cadd(t, b);
+  b = csub(t, b);
+}
+
+template <bool INV>
+PS_HD void dft4(cf& a, cf& b, cf& c, cf& d) {
+  cf t0 = cadd(a, c), t1 = csub(a, c), t2 = cadd(b, d), t3 = rot<INV>(csub(b, d));
+  a = cadd(t0, t2);
+  c = csub(t0, t2);
+  b = cadd(t1, t3);
+  d = csub(t1, t3);
+}
+
+#define PS_SQH 0.70710678118654752440f
+#define PS_C16 0.92387953251128675613f
+#define PS_S16 0.38268343236508977173f
+
+// v[k] <- sum_a v[a] W8^(a*k), natural order in and out
+template <bool INV>
+PS_HD void dft8(cf* v) {
+  // a = a0 + 2*a1: radix-4 over a1 for a0 = 0,1
+  dft4<INV>(v[0], v[2], v[4], v[6]);  // T[0][ka] at v[2*ka]
+  dft4<INV>(v[1], v[3], v[5], v[7]);  // T[1][ka] at v[2*ka+1]
+  // twiddle T[1][ka] *= W8^ka
+  const float s = INV ? PS_SQH : -PS_SQH;
+  v[3] = cmul(v[3], mk(PS_SQH, s));
+  v[5] = rot<INV>(v[5]);
+  v[7] = cmul(v[7], mk(-PS_SQH, s));
+  cf o[8];
+#pragma unroll
+  for (int ka = 0; ka < 4; ka++) {
+    o[ka] = cadd(v[2 * ka], v[2 * ka + 1]);
+    o[ka + 4] = csub(v[2 * ka], v[2 * ka + 1]);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) v[i] = o[i];
+}
+
+template <bool INV>
+PS_HD void dft16(cf* v) {
+  // a = a0 + 4*a1, k = ka + 4*kb : radix-4 over a1 (per a0), twiddle W16^(a0*ka), radix-4 over a0
+#pragma unroll
+  for (int a0 = 0; a0 < 4; a0++) dft4<INV>(v[a0], v[a0 + 4], v[a0 + 8], v[a0 + 12]);
+  // now T[a0][ka] at v[a0 + 4*ka]
+  const float sg = INV ? 1.f : -1.f;
+  v[1 + 4 * 1] = cmul(v[1 + 4 * 1], mk(PS_C16, sg * PS_S16));   // W16^1
+  v[1 + 4 * 2] = cmul(v[1 + 4 * 2], mk(PS_SQH, sg * PS_SQH));   // W16^2
+  v[1 + 4 * 3] = cmul(v[1 + 4 * 3], mk(PS_S16, sg * PS_C16));   // W16^3
+  v[2 + 4 * 1] = cmul(v[2 + 4 * 1], mk(PS_SQH, sg * PS_SQH));   // W16^2
+  v[2 + 4 * 2] = rot<INV>(v[2 + 4 * 2]);                        // W16^4
+  v[2 + 4 * 3] = cmul(v[2 + 4 * 3], mk(-PS_SQH, sg * PS_SQH));  // W16^6
+  v[3 + 4 * 1] = cmul(v[3 + 4 * 1], mk(PS_S16, sg * PS_C16));   // W16^3
+  v[3 + 4 * 2] = cmul(v[3 + 4 * 2], mk(-PS_SQH, sg * PS_SQH));  // W16^6
+  v[3 + 4 * 3] = cmul(v[3 + 4 * 3], mk(-PS_C16, -sg * PS_S16)); // W16^9
+  cf o[16];
+#pragma unroll
+  for (int ka = 0; ka < 4; ka++) {
+    cf a = v[0 + 4 * ka], b = v[1 + 4 * ka], c = v[2 + 4 * ka], d = v[3 + 4 * ka];
+    dft4<INV>(a, b, c, d);  // over a0 -> kb
+    o[ka + 4 * 0] = a;
+    o[ka + 4 * 1] = b;
+    o[ka + 4 * 2] = c;
+    o[ka + 4 * 3] = d;
+  }
+#pragma unroll
+  for (int i = 0; i < 16; i++) v[i] = o[i];
+}
+
+template <int R, bool INV>
+PS_HD void dftR(cf* v) {
+  if constexpr (R == 2) dft2<INV>(v[0], v[1]);
+  if constexpr (R == 4) dft4<INV>(v[0], v[1], v[2], v[3]);
+  if constexpr (R == 8) dft8<INV>(v);
+  if constexpr (R == 16) dft16<INV>(v);
+}
+
+// v[k] *= w^k for k = 1..15, powers built as a balanced product tree (error ~log2(k) ulp)
+PS_HD void twiddle_powers16(cf* v, cf w1) {
+  cf w[16];
+  w[1] = w1;
+#pragma unroll
+  for (int k = 2; k < 16; k++) w[k] = cmul(w[k / 2], w[k - k / 2]);
+#pragma unroll
+  for (int k = 1; k < 16; k++) v[k] = cmul(v[k], w[k]);
+}
+
+// One CTA-wide batch of F FFTs of length n = 256*R3.  512 threads; thread t = u*F + f.
+template <int R3, bool INV>
+struct CtaFft {
+  static constexpr int F = 32 / R3;
+  static constexpr int G = 16 * R3;      // threads per FFT
+  static constexpr int N = 256 * R3;     // FFT length
+  static constexpr int THREADS = F * G;  // 512
+  static constexpr int E1_WORDS = 16 * G * F;
+  static constexpr int E2_WORDS = (R3 > 1) ? 256 * (R3 + 1) * F : 0;
+  static constexpr int SMEM_WORDS = 2 * (E1_WORDS + E2_WORDS);  // re+im planes
+  static constexpr size_t SMEM_BYTES = sizeof(float) * SMEM_WORDS;
+
+  // W4096[q] = exp(-2*pi*i*q/4096), q in [0,4096)
+  template <class Loader>
+  PS_HD static void phaseA(int t, float* s, const cf* W4096, const Loader& ld) {
+    const int f = t % F, u = t / F;
+    float* e1r = s;
+    float* e1i = s + E1_WORDS;
+    cf v[16];
+#pragma unroll
+    for (int a = 0; a < 16; a++) v[a] = ld(f, a * G + u);
+    dft16<INV>(v);
+    cf w1 = ldg_cf(&W4096[u * (4096 / N)]);
+    cf wd = dirw<INV>(w1);
+    twiddle_powers16(v, wd);
+#pragma unroll
+    for (int ka = 0; ka < 16; ka++) {
+      e1r[(ka * G + u) * F + f] = v[ka].x;
+      e1i[(ka * G + u) * F + f] = v[ka].y;
+    }
+  }
+
+  template <class Storer>
+  PS_HD static void phaseB(int t, float* s, const cf* W4096, const Storer& st) {
+    const int f = t % F, u = t / F;
+    const int ka = u / R3, c = u % R3;
+    const float* e1r = s;
+    const float* e1i = s + E1_WORDS;
+    cf v[16];
+#pragma unroll
+    for (int b = 0; b < 16; b++) {
+      int a = (ka * G + b * R3 + c) * F + f;
+      v[b] = mk(e1r[a], e1i[a]);
+    }
+    dft16<INV>(v);
+    if (R3 == 1) {
+#pragma unroll
+      for (int kb = 0; kb < 16; kb++) st(f, ka + 16 * kb, v[kb]);
+      return;
+    }
+    cf w1 = ldg_cf(&W4096[c * (256 / R3)]);  // W_(16*R3)^c
+    twiddle_powers16(v, dirw<INV>(w1));
+    float* e2r = s + 2 * E1_WORDS;
+    float* e2i = e2r + E2_WORDS;
+#pragma unroll
+    for (int kb = 0; kb < 16; kb++) {
+      int a = ((ka + 16 * kb) * (R3 + 1) + c) * F + f;
+      e2r[a] = v[kb].x;
+      e2i[a] = v[kb].y;
+    }
+  }
+
+  template <class Storer>
+  PS_HD static void phaseC(int t, const float* s, const Storer& st) {
+    if (R3 == 1) return;
+    const int f = t % F, u = t / F;
+    const float* e2r = s + 2 * E1_WORDS;
+    const float* e2i = e2r + E2_WORDS;
+    constexpr int RR = (R3 > 1) ? R3 : 2;
+#pragma unroll
+    for (int m = 0; m < 16 / RR; m++) {
+      const int q = u + G * m;
+      cf w[RR];
+#pragma unroll
+      for (int c = 0; c < RR; c++) {
+        int a = (q * (R3 + 1) + c) * F + f;
+        w[c] = mk(e2r[a], e2i[a]);
+      }
+      dftR<RR, INV>(w);
+#pragma unroll
+      for (int kc = 0; kc < RR; kc++) st(f, q + 256 * kc, w[kc]);
+    }
+  }
+};
+
+}  // namespace psfft
