@@ -148,6 +148,53 @@ const float* ps_search_last_spectrum(ps_search* s);     /* size/2+1 floats (last
 /* kernel launch counter (all ps_* kernels launched by this process; for bench.py) */
 unsigned long long ps_launch_count(void);
 
+/* ---------------- pipeline driver + host-side logic ----------------------------------- */
+typedef struct {
+  ps_search_params search;
+  float freq_tol;        /* --freq_tol */
+  int max_harm;          /* --max_harm_match */
+  /* AccelerationPlan (utils.hpp:140-193); used when no explicit acceleration list is given */
+  float acc_start, acc_end, acc_tol, acc_pulse_width;
+  float cfreq, foff;     /* filterbank centre frequency / channel width (MHz) */
+} ps_pipeline_params;
+
+typedef struct {
+  float dm;
+  int32_t dm_idx;
+  float acc;
+  int32_t nh;
+  float snr;
+  float freq;
+  int32_t is_top; /* 1: entry of dm_trial_cands; 0: member of the preceding entry's assoc list */
+} ps_candidate;
+
+/* Worker::start + thread fan-out (pipeline_multi.cu:100-252, 342-359) over `ndm` host-resident
+ * 8-bit trials [ndm][nsamps], on devices device0 .. device0+nworkers-1 (one host thread each,
+ * dynamic DM dispatch).  Candidates of all workers are concatenated in ascending dm_idx order
+ * (the reference's -t 1 order) and flattened depth-first like Candidate::collect_candidates.
+ * dm_idx_offset is added to every dm_idx (for DM-sharded multi-process runs).
+ * Returns the number of records (may exceed max_out: then only max_out were written) or <0.
+ * trials_done (optional) receives the number of DM x acceleration trials searched. */
+long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_trials, const float* h_dm_list,
+                        int ndm, int dm_idx_offset, const float* h_acc_explicit, int n_acc_explicit,
+                        const float* h_zap_freqs, const float* h_zap_widths, int nzap, int device0,
+                        int nworkers, ps_candidate* out, long max_out, unsigned long long* trials_done);
+
+/* AccelerationPlan::generate_accel_list (utils.hpp:168-192).  Returns the list length. */
+int ps_accel_plan_generate(float acc_lo, float acc_hi, float tol, float pulse_width, unsigned nsamps,
+                           float tsamp, float cfreq, float bw, float dm, float* out, int max_out);
+/* PeakFinder::identify_unique_peaks (peakfinder.hpp:27-56). Returns the number of clusters. */
+int ps_cluster_peaks(const int* idxs, const float* snrs, int count, int min_gap, int* out_idx,
+                     float* out_snr);
+/* PeakFinder::find_candidates bin range / frequency factor (peakfinder.hpp:77-92). */
+int ps_peak_range(int nbins, double bin_width, int nh, float min_freq, float max_freq, int* start_idx,
+                  int* limit, float* factor);
+/* Distillers (distiller.hpp): kind 0 = HarmonicDistiller(tol,max_harm,keep_related,fractional),
+ * 1 = AccelerationDistiller(tobs,tol,keep_related), 2 = DMDistiller(tol,keep_related).
+ * in: n candidates (is_top ignored); out: flattened survivors (+ assoc if keep_related). */
+long ps_distill(int kind, float tol, float max_harm_or_tobs, int keep_related, int fractional_harms,
+                const ps_candidate* in, long n, ps_candidate* out, long max_out);
+
 #ifdef __cplusplus
 }
 #endif

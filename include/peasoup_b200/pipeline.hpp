@@ -1,0 +1,192 @@
+// pipeline.hpp -- host-side mirror of the reference's multi-GPU search driver
+// (src/pipeline_multi.cu:33-259: DMDispenser, Worker, launch_worker_thread).
+//
+// Worker::start keeps the reference's statement order per DM trial
+//   copy trial -> [pad] -> accel list -> whiten (R2C, |X|, running median, deredden, zap,
+//   interbin, stats, C2R) -> for each acceleration: resample, R2C, interbin, normalise,
+//   harmonic sums, peaks, harmonic distill -> acceleration distill
+// but drives the fused device path (ps_search_*): all device work of a DM trial is queued on
+// one stream without host synchronisation, two DM trials are in flight per worker (double
+// buffering), and the host-side clustering/distillation of trial i overlaps the device work of
+// trial i+1.  Candidate output is identical in content and order to the staged path.
+#pragma once
+#include <mutex>
+#include <thread>
+#include "transforms.hpp"
+
+namespace peasoup_b200 {
+
+// subset of CmdLineOptions (utils/cmdline.hpp:12-47) read by the Worker
+struct SearchArgs {
+  unsigned int size = 0;       // --fft_size (0: prev_power_of_two(nsamps))
+  int nharmonics = 4;          // -n: number of folds
+  float min_snr = 9.0f;        // -m
+  float min_freq = 0.1f;       // --min_freq
+  float max_freq = 1100.0f;    // --max_freq
+  float freq_tol = 1e-4f;      // --freq_tol
+  int max_harm = 16;           // --max_harm_match
+  std::string zapfilename;     // -z
+  std::vector<float> zap_freqs, zap_widths;  // alternative to zapfilename
+  unsigned int max_peaks = 0;  // raw above-threshold bins kept per DM trial (0 -> 1<<20)
+  bool verbose = false;
+};
+
+class DMDispenser {  // pipeline_multi.cu:33-81 (progress bar omitted)
+  std::mutex mutex;
+  int dm_idx;
+  int count;
+
+ public:
+  template <class Trials>
+  explicit DMDispenser(Trials& trials) : dm_idx(0), count((int)trials.get_count()) {}
+  explicit DMDispenser(int count) : dm_idx(0), count(count) {}
+  int get_dm_trial_idx() {
+    std::lock_guard<std::mutex> lk(mutex);
+    if (dm_idx >= count) return -1;
+    return dm_idx++;
+  }
+};
+
+class Worker {  // pipeline_multi.cu:83-254
+  DispersionTrials<unsigned char>& trials;
+  DMDispenser& manager;
+  SearchArgs& args;
+  AccelerationPlan& acc_plan;
+  unsigned int size;
+  int device;
+  const std::vector<float>* fixed_accs;  // when set, replaces acc_plan (benchmarks / parity harness)
+  int dm_idx_offset;
+
+  struct Slot {
+    ps_search* search = 0;
+    cudaStream_t stream = 0;
+    unsigned char* d_trial = 0;
+    std::vector<ps_raw_peak> peaks;
+    std::vector<float> acc_list;
+    int ii = -1;
+    float dm = 0.f;
+  };
+
+ public:
+  CandidateCollection dm_trial_cands;
+  unsigned long long trials_done = 0;  // DM x acceleration trials searched
+
+  Worker(DispersionTrials<unsigned char>& trials, DMDispenser& manager, AccelerationPlan& acc_plan, SearchArgs& args,
+         unsigned int size, int device, const std::vector<float>* fixed_accs = 0, int dm_idx_offset = 0)
+      : trials(trials), manager(manager), args(args), acc_plan(acc_plan), size(size), device(device), fixed_accs(fixed_accs),
+        dm_idx_offset(dm_idx_offset) {}
+
+  void start() {
+    ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
+    ps_search_params prm;
+    prm.size = size;
+    prm.nsamps = trials.get_nsamps();
+    prm.tsamp = trials.get_tsamp();
+    prm.nharmonics = args.nharmonics;
+    prm.min_snr = args.min_snr;
+    prm.min_freq = args.min_freq;
+    prm.max_freq = args.max_freq;
+    prm.boundary_5_freq = 0.05f;
+    prm.boundary_25_freq = 0.5f;
+    prm.max_peaks = args.max_peaks;
+    const unsigned cap = prm.max_peaks ? prm.max_peaks : (1u << 20);
+
+    std::vector<float> zf = args.zap_freqs, zw = args.zap_widths;
+    if (args.zapfilename != "") Zapper::parse(args.zapfilename, zf, zw);
+
+    float tobs = size * trials.get_tsamp();  // pipeline_multi.cu:118
+    float bin_width_f = 1.0 / tobs;          // :119
+    double bin_width = bin_width_f;
+    const unsigned nbins = size / 2 + 1;
+    std::vector<PeakRange> ranges;
+    for (int nh = 0; nh <= args.nharmonics; nh++) ranges.push_back(peak_range((int)nbins, bin_width, nh, args.min_freq, args.max_freq));
+    HarmonicDistiller harm_finder(args.freq_tol, args.max_harm, false);  // :138
+    AccelerationDistiller acc_still(tobs, args.freq_tol, true);          // :139
+    const size_t ncopy = std::min(trials.get_nsamps(), size);
+
+    Slot slots[2];
+    struct Cleanup {
+      Slot* s;
+      ~Cleanup() {
+        for (int i = 0; i < 2; i++) {
+          if (s[i].stream) cudaStreamSynchronize(s[i].stream);
+          ps_search_destroy(s[i].search);
+          cudaFree(s[i].d_trial);
+          if (s[i].stream) cudaStreamDestroy(s[i].stream);
+        }
+      }
+    } cleanup{slots};
+    for (int i = 0; i < 2; i++) {
+      ErrorChecker::check(ps_search_create(&prm, &slots[i].search));
+      if (!zf.empty()) ErrorChecker::check(ps_search_set_zaplist(slots[i].search, &zf[0], &zw[0], (unsigned)zf.size()));
+      ErrorChecker::check_cuda_error(cudaStreamCreateWithFlags(&slots[i].stream, cudaStreamNonBlocking), "cudaStreamCreate");
+      Utils::device_malloc(&slots[i].d_trial, ncopy);
+      slots[i].peaks.resize(cap);
+    }
+
+    std::vector<int> idxs, peakidxs;
+    std::vector<float> snrs, peaksnrs, peakfreqs;
+
+    auto submit = [&](Slot& s) -> bool {
+      s.ii = manager.get_dm_trial_idx();
+      if (s.ii == -1) return false;
+      DedispersedTimeSeries<unsigned char> tim;
+      trials.get_idx(s.ii, tim);
+      s.dm = tim.get_dm();
+      ErrorChecker::check_cuda_error(
+          cudaMemcpyAsync(s.d_trial, tim.get_data(), ncopy, cudaMemcpyHostToDevice, s.stream), "Error from h2dcpy");
+      if (fixed_accs)
+        s.acc_list = *fixed_accs;
+      else
+        acc_plan.generate_accel_list(s.dm, s.acc_list);
+      ErrorChecker::check(ps_search_reset_peaks(s.search, s.stream));
+      ErrorChecker::check(ps_search_whiten(s.search, s.d_trial, 0, 0, s.stream));
+      ErrorChecker::check(ps_search_accel_batch(s.search, &s.acc_list[0], (int)s.acc_list.size(), 0, s.stream));
+      return true;
+    };
+
+    auto finish = [&](Slot& s) {
+      long n = ps_search_fetch_peaks(s.search, &s.peaks[0], s.peaks.size(), s.stream);
+      ErrorChecker::check((int)std::min<long>(n, 0));
+      CandidateCollection accel_trial_cands;
+      long pos = 0;
+      for (int jj = 0; jj < (int)s.acc_list.size(); jj++) {
+        SpectrumCandidates trial_cands(s.dm, s.ii + dm_idx_offset, s.acc_list[jj]);
+        for (int nh = 0; nh <= args.nharmonics; nh++) {
+          idxs.clear();
+          snrs.clear();
+          for (; pos < n && s.peaks[pos].acc_idx == jj && s.peaks[pos].nh == nh; pos++) {
+            idxs.push_back(s.peaks[pos].bin);
+            snrs.push_back(s.peaks[pos].snr);
+          }
+          if (idxs.empty()) continue;
+          peakidxs.resize(idxs.size());
+          peaksnrs.resize(idxs.size());
+          peakfreqs.resize(idxs.size());
+          int npeaks = cluster_peaks(&idxs[0], &snrs[0], (int)idxs.size(), 30, &peakidxs[0], &peaksnrs[0]);
+          for (int k = 0; k < npeaks; k++) peakfreqs[k] = peakidxs[k] * ranges[nh].factor;
+          trial_cands.append(&peaksnrs[0], &peakfreqs[0], nh, npeaks);
+        }
+        accel_trial_cands.append(harm_finder.distill(trial_cands.cands));
+      }
+      dm_trial_cands.append(acc_still.distill(accel_trial_cands.cands));
+      trials_done += s.acc_list.size();
+    };
+
+    int cur = 0;
+    bool live = submit(slots[cur]);
+    while (live) {
+      bool next_live = submit(slots[cur ^ 1]);
+      finish(slots[cur]);
+      cur ^= 1;
+      live = next_live;
+    }
+  }
+};
+
+inline void* launch_worker_thread(void* ptr) {  // pipeline_multi.cu:256-259
+  reinterpret_cast<Worker*>(ptr)->start();
+  return NULL;
+}
+
+}  // namespace peasoup_b200

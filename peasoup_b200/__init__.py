@@ -1,0 +1,133 @@
+"""peasoup_b200 -- ctypes binding of libpeasoup_b200.so (the C ABI in include/peasoup_b200.h).
+
+Python is plumbing only (device memory through torch tensors, process launch, tests and
+bench); every computation is a hand-written sm_100a kernel inside the shared library.  There
+is no CPU fallback: if the library is missing, ``load()`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+_ROOT = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(_ROOT)
+LIB_PATH = os.path.join(_ROOT, "lib", "libpeasoup_b200.so")
+_lib = None
+
+
+class PeasoupError(RuntimeError):
+    pass
+
+
+class SearchParams(C.Structure):
+    _fields_ = [("size", C.c_uint), ("nsamps", C.c_uint), ("tsamp", C.c_float), ("nharmonics", C.c_int),
+                ("min_snr", C.c_float), ("min_freq", C.c_float), ("max_freq", C.c_float),
+                ("boundary_5_freq", C.c_float), ("boundary_25_freq", C.c_float), ("max_peaks", C.c_uint)]
+
+
+class PipelineParams(C.Structure):
+    _fields_ = [("search", SearchParams), ("freq_tol", C.c_float), ("max_harm", C.c_int),
+                ("acc_start", C.c_float), ("acc_end", C.c_float), ("acc_tol", C.c_float),
+                ("acc_pulse_width", C.c_float), ("cfreq", C.c_float), ("foff", C.c_float)]
+
+
+class RawPeak(C.Structure):
+    _fields_ = [("acc_idx", C.c_int32), ("nh", C.c_int32), ("bin", C.c_int32), ("snr", C.c_float)]
+
+
+class Candidate(C.Structure):
+    _fields_ = [("dm", C.c_float), ("dm_idx", C.c_int32), ("acc", C.c_float), ("nh", C.c_int32),
+                ("snr", C.c_float), ("freq", C.c_float), ("is_top", C.c_int32)]
+
+
+# every symbol include/peasoup_b200.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "ps_last_error", "ps_version", "ps_resampleII", "ps_resample", "ps_resample_index_map",
+    "ps_form_power_series", "ps_normalise", "ps_harmonic_sum", "ps_peak_workspace_create",
+    "ps_peak_workspace_destroy", "ps_find_peaks", "ps_median_scrunch5", "ps_linear_stretch",
+    "ps_running_median", "ps_divide_c_by_f", "ps_zap_birdies", "ps_rms", "ps_mean", "ps_fill",
+    "ps_convert_u8_f32", "ps_fft_plan_create", "ps_fft_plan_destroy", "ps_fft_r2c", "ps_fft_c2r",
+    "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
+    "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks",
+    "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_pipeline_search",
+    "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
+]
+
+
+def build(verbose: bool = False) -> None:
+    """Compile libpeasoup_b200.so in-tree with nvcc for sm_100a (see Makefile)."""
+    r = subprocess.run(["make", "-C", REPO, "all"], capture_output=True, text=True)
+    if verbose or r.returncode:
+        print(r.stdout[-4000:], r.stderr[-4000:])
+    if r.returncode:
+        raise PeasoupError("building libpeasoup_b200.so failed")
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise PeasoupError(f"{LIB_PATH} is missing: run `make` (or __graft_entry__.build()); there is no CPU fallback")
+    lib = C.CDLL(LIB_PATH)
+    vp, i, u, f, sz, d = C.c_void_p, C.c_int, C.c_uint, C.c_float, C.c_size_t, C.c_double
+    lib.ps_last_error.restype = C.c_char_p
+    lib.ps_launch_count.restype = C.c_ulonglong
+    sig = {
+        "ps_resampleII": [vp, vp, sz, f, f, vp], "ps_resample": [vp, vp, sz, f, f, vp],
+        "ps_resample_index_map": [vp, sz, f, f, i, vp],
+        "ps_form_power_series": [vp, vp, sz, i, vp], "ps_normalise": [vp, f, f, u, vp],
+        "ps_harmonic_sum": [vp, C.POINTER(vp), sz, u, vp],
+        "ps_peak_workspace_create": [sz, C.POINTER(vp)], "ps_peak_workspace_destroy": [vp],
+        "ps_find_peaks": [i, i, vp, f, vp, vp, sz, vp, vp],
+        "ps_median_scrunch5": [vp, sz, vp, vp], "ps_linear_stretch": [vp, sz, vp, sz, vp],
+        "ps_running_median": [vp, u, d, f, f, vp, vp, vp],
+        "ps_divide_c_by_f": [vp, vp, u, vp], "ps_zap_birdies": [vp, vp, vp, f, u, u, vp],
+        "ps_rms": [vp, i, i, C.POINTER(f)], "ps_mean": [vp, i, i, C.POINTER(f)], "ps_fill": [vp, vp, f, vp],
+        "ps_convert_u8_f32": [vp, vp, u, vp],
+        "ps_fft_plan_create": [u, C.POINTER(vp)], "ps_fft_plan_destroy": [vp],
+        "ps_fft_r2c": [vp, vp, vp, vp], "ps_fft_c2r": [vp, vp, vp, vp],
+        "ps_search_create": [C.POINTER(SearchParams), C.POINTER(vp)], "ps_search_destroy": [vp],
+        "ps_search_set_zaplist": [vp, vp, vp, u],
+        "ps_search_whiten": [vp, vp, C.POINTER(f), C.POINTER(f), vp],
+        "ps_search_accel_batch": [vp, vp, i, i, vp], "ps_search_reset_peaks": [vp, vp],
+        "ps_search_fetch_peaks": [vp, vp, sz, vp],
+        "ps_search_whitened_series": [vp], "ps_search_last_spectrum": [vp],
+        "ps_pipeline_search": [C.POINTER(PipelineParams), vp, vp, i, i, vp, i, vp, vp, i, i, i, vp, C.c_long,
+                               C.POINTER(C.c_ulonglong)],
+        "ps_accel_plan_generate": [f, f, f, f, u, f, f, f, f, vp, i],
+        "ps_cluster_peaks": [vp, vp, i, i, vp, vp],
+        "ps_peak_range": [i, d, i, f, f, C.POINTER(i), C.POINTER(i), C.POINTER(f)],
+        "ps_distill": [i, f, f, i, i, vp, C.c_long, vp, C.c_long],
+    }
+    for name, args in sig.items():
+        getattr(lib, name).argtypes = args
+    lib.ps_search_fetch_peaks.restype = C.c_long
+    lib.ps_pipeline_search.restype = C.c_long
+    lib.ps_distill.restype = C.c_long
+    lib.ps_search_whitened_series.restype = vp
+    lib.ps_search_last_spectrum.restype = vp
+    lib.ps_peak_workspace_destroy.restype = None
+    lib.ps_fft_plan_destroy.restype = None
+    lib.ps_search_destroy.restype = None
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> int:
+    """Raise PeasoupError (with ps_last_error) on a negative status; pass counts through."""
+    if rc < 0:
+        raise PeasoupError(load().ps_last_error().decode(errors="replace"))
+    return rc
+
+
+def ptr(t) -> int:
+    """Device/host pointer of a torch tensor or numpy array as an int."""
+    if hasattr(t, "data_ptr"):
+        return t.data_ptr()
+    return t.ctypes.data
+
+
+from .host import (FFTPlan, Search, accel_plan, cluster_peaks, distill, peak_range,  # noqa: E402
+                   pipeline_search)

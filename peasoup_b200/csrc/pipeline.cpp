@@ -1,0 +1,144 @@
+// pipeline.cpp -- C-ABI entry points over the C++ host mirror (include/peasoup_b200/*.hpp):
+// the Worker fan-out of src/pipeline_multi.cu:342-359 and test hooks for the host-side logic.
+#include <exception>
+#include <string>
+#include <thread>
+#include "../../include/peasoup_b200/pipeline.hpp"
+
+namespace ps {
+void set_error(const std::string& msg);
+}
+using namespace peasoup_b200;
+
+static long flatten(std::vector<Candidate>& cands, ps_candidate* out, long max_out) {
+  long n = 0;
+  for (size_t i = 0; i < cands.size(); i++) {
+    std::vector<CandidatePOD> flat;
+    cands[i].collect_candidates(flat);
+    for (size_t k = 0; k < flat.size(); k++, n++) {
+      if (n >= max_out) continue;
+      out[n].dm = flat[k].dm;
+      out[n].dm_idx = flat[k].dm_idx;
+      out[n].acc = flat[k].acc;
+      out[n].nh = flat[k].nh;
+      out[n].snr = flat[k].snr;
+      out[n].freq = flat[k].freq;
+      out[n].is_top = k == 0;
+    }
+  }
+  return n;
+}
+
+extern "C" {
+
+long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_trials, const float* h_dm_list, int ndm,
+                        int dm_idx_offset, const float* h_acc_explicit, int n_acc_explicit, const float* h_zap_freqs,
+                        const float* h_zap_widths, int nzap, int device0, int nworkers, ps_candidate* out, long max_out,
+                        unsigned long long* trials_done) {
+  try {
+    if (!p || (!h_trials && ndm > 0)) ErrorChecker::throw_error("ps_pipeline_search: null argument");
+    if (nworkers < 1) nworkers = 1;
+    std::vector<float> dms(h_dm_list, h_dm_list + ndm);
+    DispersionTrials<unsigned char> trials(const_cast<unsigned char*>(h_trials), p->search.nsamps, p->search.tsamp, dms);
+    SearchArgs args;
+    args.size = p->search.size;
+    args.nharmonics = p->search.nharmonics;
+    args.min_snr = p->search.min_snr;
+    args.min_freq = p->search.min_freq;
+    args.max_freq = p->search.max_freq;
+    args.freq_tol = p->freq_tol;
+    args.max_harm = p->max_harm;
+    args.max_peaks = p->search.max_peaks;
+    if (nzap > 0) {
+      args.zap_freqs.assign(h_zap_freqs, h_zap_freqs + nzap);
+      args.zap_widths.assign(h_zap_widths, h_zap_widths + nzap);
+    }
+    unsigned size = args.size ? args.size : Utils::prev_power_of_two(p->search.nsamps);
+    AccelerationPlan acc_plan(p->acc_start, p->acc_end, p->acc_tol, p->acc_pulse_width, size, p->search.tsamp, p->cfreq, p->foff);
+    std::vector<float> fixed;
+    if (n_acc_explicit > 0) fixed.assign(h_acc_explicit, h_acc_explicit + n_acc_explicit);
+    DMDispenser dispenser(trials);
+    std::vector<Worker*> workers;
+    std::vector<std::thread> threads;
+    std::vector<std::exception_ptr> errors(nworkers);
+    for (int i = 0; i < nworkers; i++)
+      workers.push_back(new Worker(trials, dispenser, acc_plan, args, size, device0 + i, n_acc_explicit > 0 ? &fixed : 0, dm_idx_offset));
+    for (int i = 0; i < nworkers; i++)
+      threads.emplace_back([&, i]() {
+        try {
+          workers[i]->start();
+        } catch (...) {
+          errors[i] = std::current_exception();
+        }
+      });
+    for (auto& t : threads) t.join();
+    CandidateCollection dm_cands;
+    unsigned long long done = 0;
+    for (int i = 0; i < nworkers; i++) {
+      dm_cands.append(workers[i]->dm_trial_cands.cands);
+      done += workers[i]->trials_done;
+    }
+    for (int i = 0; i < nworkers; i++) delete workers[i];
+    for (int i = 0; i < nworkers; i++)
+      if (errors[i]) std::rethrow_exception(errors[i]);
+    // canonical order = ascending dm_idx, emission order within a DM trial (the reference's -t 1 run)
+    std::stable_sort(dm_cands.cands.begin(), dm_cands.cands.end(),
+                     [](const Candidate& a, const Candidate& b) { return a.dm_idx < b.dm_idx; });
+    if (trials_done) *trials_done = done;
+    return flatten(dm_cands.cands, out, max_out);
+  } catch (std::exception& e) {
+    ps::set_error(e.what());
+    return PS_ECUDA;
+  }
+}
+
+int ps_accel_plan_generate(float acc_lo, float acc_hi, float tol, float pulse_width, unsigned nsamps, float tsamp,
+                           float cfreq, float bw, float dm, float* out, int max_out) {
+  AccelerationPlan plan(acc_lo, acc_hi, tol, pulse_width, nsamps, tsamp, cfreq, bw);
+  std::vector<float> l;
+  plan.generate_accel_list(dm, l);
+  for (int i = 0; i < (int)l.size() && i < max_out; i++) out[i] = l[i];
+  return (int)l.size();
+}
+
+int ps_cluster_peaks(const int* idxs, const float* snrs, int count, int min_gap, int* out_idx, float* out_snr) {
+  return cluster_peaks(idxs, snrs, count, min_gap, out_idx, out_snr);
+}
+
+int ps_peak_range(int nbins, double bin_width, int nh, float min_freq, float max_freq, int* start_idx, int* limit,
+                  float* factor) {
+  PeakRange r = peak_range(nbins, bin_width, nh, min_freq, max_freq);
+  *start_idx = r.start_idx;
+  *limit = r.limit;
+  *factor = r.factor;
+  return PS_OK;
+}
+
+long ps_distill(int kind, float tol, float max_harm_or_tobs, int keep_related, int fractional_harms, const ps_candidate* in,
+                long n, ps_candidate* out, long max_out) {
+  try {
+    std::vector<Candidate> c;
+    c.reserve(n);
+    for (long i = 0; i < n; i++) c.push_back(Candidate(in[i].dm, in[i].dm_idx, in[i].acc, in[i].nh, in[i].snr, in[i].freq));
+    std::vector<Candidate> r;
+    if (kind == 0) {
+      HarmonicDistiller d(tol, max_harm_or_tobs, keep_related != 0, fractional_harms != 0);
+      r = d.distill(c);
+    } else if (kind == 1) {
+      AccelerationDistiller d(max_harm_or_tobs, tol, keep_related != 0);
+      r = d.distill(c);
+    } else if (kind == 2) {
+      DMDistiller d(tol, keep_related != 0);
+      r = d.distill(c);
+    } else {
+      ps::set_error("ps_distill: unknown kind");
+      return PS_EINVAL;
+    }
+    return flatten(r, out, max_out);
+  } catch (std::exception& e) {
+    ps::set_error(e.what());
+    return PS_ECUDA;
+  }
+}
+
+}  // extern "C"
