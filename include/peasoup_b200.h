@@ -147,6 +147,9 @@ const float* ps_search_whitened_series(ps_search* s);   /* size floats */
 const float* ps_search_last_spectrum(ps_search* s);     /* size/2+1 floats (last accel trial) */
 /* kernel launch counter (all ps_* kernels launched by this process; for bench.py) */
 unsigned long long ps_launch_count(void);
+/* host<->device traffic issued by the pipeline driver: add to / read the process-wide counters */
+void ps_count_transfer(unsigned long long h2d_bytes, unsigned long long d2h_bytes);
+void ps_transfer_bytes(unsigned long long* h2d_bytes, unsigned long long* d2h_bytes);
 
 /* ---------------- pipeline driver + host-side logic ----------------------------------- */
 typedef struct {

@@ -133,8 +133,11 @@ class Worker {  // pipeline_multi.cu:83-254
       DedispersedTimeSeries<unsigned char> tim;
       trials.get_idx(s.ii, tim);
       s.dm = tim.get_dm();
+      // cudaMemcpyDefault: the trials may live in (pinned or pageable) host memory, as in the
+      // reference, or already in device memory (bench.py's HBM-resident measurement)
       ErrorChecker::check_cuda_error(
-          cudaMemcpyAsync(s.d_trial, tim.get_data(), ncopy, cudaMemcpyHostToDevice, s.stream), "Error from h2dcpy");
+          cudaMemcpyAsync(s.d_trial, tim.get_data(), ncopy, cudaMemcpyDefault, s.stream), "Error from h2dcpy");
+      ps_count_transfer(ncopy, 0);
       if (fixed_accs)
         s.acc_list = *fixed_accs;
       else

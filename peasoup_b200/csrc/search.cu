@@ -317,8 +317,12 @@ long ps_search_fetch_peaks(ps_search* hs, ps_raw_peak* h_out, size_t max_out, vo
     set_error("ps_search_fetch_peaks: more above-threshold bins than the peak list holds (raise max_peaks)");
     return PS_EOVERFLOW;
   }
-  if (!count) return 0;
+  if (!count) {
+    ps_count_transfer(0, sizeof(unsigned));
+    return 0;
+  }
   PS_CUDA(cudaMemcpyAsync(h_out, s->d_peaks, sizeof(ps_raw_peak) * count, cudaMemcpyDeviceToHost, st), "Error from d2hcpy");
+  ps_count_transfer(0, sizeof(unsigned) + sizeof(ps_raw_peak) * (unsigned long long)count);
   PS_CUDA(cudaStreamSynchronize(st), "ps_search_fetch_peaks");
   std::sort(h_out, h_out + count, [](const ps_raw_peak& a, const ps_raw_peak& b) {
     if (a.acc_idx != b.acc_idx) return a.acc_idx < b.acc_idx;

@@ -269,6 +269,15 @@ extern "C" {
 const char* ps_last_error(void) { return ps::t_err.c_str(); }
 int ps_version(void) { return 100; }
 unsigned long long ps_launch_count(void) { return ps::g_launches.load(); }
+static std::atomic<unsigned long long> g_h2d{0}, g_d2h{0};
+void ps_count_transfer(unsigned long long h2d, unsigned long long d2h) {
+  g_h2d.fetch_add(h2d, std::memory_order_relaxed);
+  g_d2h.fetch_add(d2h, std::memory_order_relaxed);
+}
+void ps_transfer_bytes(unsigned long long* h2d, unsigned long long* d2h) {
+  if (h2d) *h2d = g_h2d.load();
+  if (d2h) *d2h = g_d2h.load();
+}
 
 int ps_resampleII(const float* d_in, float* d_out, size_t n, float a, float tsamp, void* stream) {
   if (!n) return PS_OK;

@@ -134,7 +134,7 @@ __device__ __forceinline__ bool zap_range(float freq, float width, float bin_wid
   int high_bin = __float2int_ru(__fdiv_rn(__fadd_rn(freq, width), bin_width));
   if (low_bin < 0) low_bin = 0;
   if ((unsigned)low_bin >= nbins) return false;
-  if (high_bin >= (int)nbins) high_bin = (int)nbins - 1;
+  if ((unsigned)high_bin >= nbins) high_bin = (int)nbins - 1;  // int vs unsigned compare, as the reference
   *lo = low_bin;
   *hi = high_bin;
   return high_bin > low_bin;

@@ -1,0 +1,253 @@
+"""GPU parity of the fused search path (ps_search_*, ps_pipeline_search) through the C ABI:
+against the CPU oracle, against the reference's golden candidates.peasoup (BASELINE.json
+configs[0]), against the UNMODIFIED reference kernels + cuFFT replaying Worker::start on the same
+device (oracle/_ref), and -- at the full 2^23 size -- through domain properties.
+
+Tolerances (north_star): resampling index maps and peak bins bit-exact; spectra within 1e-4
+relative; candidate list (DM, accel, bin, nh) identical with S/N within 1 %.  Bins whose value
+lies within 1e-3 (relative) of the threshold may legitimately flip because FFT rounding differs
+from cuFFT's; they are classified separately and must be rare."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import peasoup_b200 as pb
+from peasoup_b200 import ptr
+from peasoup_b200.host import make_search_params
+from conftest import GOLDEN
+from synth import cand_keys, make_trials
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+SPEC_TOL = 1e-4
+SNR_TOL = 1e-2
+
+
+def dev_f32(p, n):
+    """copy n floats from a raw device pointer (zero acceleration = identity index map)"""
+    t = torch.zeros(n, dtype=torch.float32, device="cuda")
+    pb.check(pb.load().ps_resampleII(p, t.data_ptr(), n, 0.0, 1.0, None))
+    torch.cuda.synchronize()
+    return t.cpu().numpy()
+
+
+def pipeline_params(size, nsamps, tsamp, nharm=4, min_snr=9.0, max_peaks=0):
+    return pb.PipelineParams(make_search_params(size, nsamps, tsamp, nharm, min_snr, max_peaks=max_peaks), 1e-4, 16,
+                             0.0, 0.0, 1.1, 64.0, 1400.0, -1.0)
+
+
+def compare_candidates(got, want, cfg, threshold=9.0):
+    """identical (dm_idx, acc, nh, bin, is_top) sets with S/N within 1 %, except records whose S/N is
+    within 1e-3 of the threshold on either side (classified, must be < 1 % of the list)."""
+    a = cand_keys(got, cfg.nbins, cfg.bin_width_f, with_top=True)
+    b = cand_keys(want, cfg.nbins, cfg.bin_width_f, with_top=True)
+    only = set(a) ^ set(b)
+    marginal = [k for k in only if abs((a.get(k) or b.get(k)) - threshold) < 2e-3 * threshold]
+    hard = [k for k in only if k not in marginal]
+    assert not hard, (len(a), len(b), hard[:8])
+    assert len(marginal) <= max(1, len(b) // 100), marginal
+    worst = max((abs(a[k] - b[k]) / b[k] for k in set(a) & set(b)), default=0.0)
+    assert worst < SNR_TOL, worst
+    return worst, len(marginal)
+
+
+# ------------------------------------------------------------------ stage-level: whitening + spectra
+@pytest.mark.parametrize("size,nsamps,zap", [(1 << 17, (1 << 17) + 300, False), (1 << 17, 100000, True), (1 << 18, 1 << 18, True)])
+def test_whiten_and_spectrum_vs_oracle(lib, oracle, size, nsamps, zap):
+    tsamp = 64e-6
+    trial = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=20.0, amp=8.0)[0]
+    zl = (np.array([50.0, 100.0], np.float32), np.array([0.1, 0.15], np.float32)) if zap else None
+    cfg = oracle.SearchConfig(size, tsamp, zap=zl)
+    s = pb.Search(make_search_params(size, nsamps, tsamp))
+    if zap:
+        s.set_zaplist(*zl)
+    d_trial = torch.from_numpy(trial).cuda()
+    mean, std = s.whiten(d_trial, want_stats=True)
+    tim, wmean, wstd, inter = oracle.whiten(trial, cfg, return_intermediates=True)
+    got = dev_f32(s.whitened_series_ptr(), size)
+    rms = np.sqrt((tim.astype(np.float64) ** 2).mean())
+    assert np.abs(got - tim).max() / rms < SPEC_TOL
+    assert abs(mean - wmean) / wmean < 1e-5 and abs(std - wstd) / wstd < 1e-5
+    for acc in (0.0, 20.0, -35.5):
+        s.reset_peaks()
+        s.accel_batch([acc])
+        p = dev_f32(s.last_spectrum_ptr(), cfg.nbins)
+        want = oracle.accel_spectrum(tim, acc, wmean, wstd, cfg)
+        # normalised spectrum has unit variance: absolute error == error relative to spectrum rms
+        assert np.abs(p - want).max() < 20 * SPEC_TOL  # bins up to ~100 sigma; relative 1e-4 of those
+        assert np.sqrt(((p - want) ** 2).mean()) < SPEC_TOL
+    s.close()
+
+
+@pytest.mark.parametrize("size", [1 << 17, 1 << 19])
+def test_raw_peaks_vs_oracle(lib, oracle, size):
+    tsamp = 64e-6
+    thresh = 6.0  # low threshold: thousands of peaks exercise the compaction
+    trial = make_trials(1, size, size, tsamp=tsamp, a_inj=31.4, amp=10.0)[0]
+    cfg = oracle.SearchConfig(size, tsamp, min_snr=thresh)
+    s = pb.Search(make_search_params(size, size, tsamp, min_snr=thresh))
+    s.whiten(torch.from_numpy(trial).cuda())
+    accs = np.array([0.0, 31.4, -12.0], np.float32)
+    s.reset_peaks()
+    s.accel_batch(accs)
+    peaks = s.fetch_peaks()
+    tim, m, sd = oracle.whiten(trial, cfg)
+    want = {}
+    for j, acc in enumerate(accs):
+        raw = oracle.spectrum_raw_peaks(oracle.accel_spectrum(tim, acc, m, sd, cfg), cfg)
+        for nh, (idx, snr, _) in enumerate(raw):
+            for i, v in zip(idx, snr):
+                want[(j, nh, int(i))] = float(v)
+    got = {(int(r["acc_idx"]), int(r["nh"]), int(r["bin"])): float(r["snr"]) for r in peaks}
+    assert list(got) == sorted(got)  # (acc_idx, nh, bin) order
+    only = set(got) ^ set(want)
+    hard = [k for k in only if abs((got.get(k) or want.get(k)) - thresh) > 2e-3 * thresh]
+    assert not hard, hard[:5]
+    assert len(only) <= max(2, len(want) // 200)
+    assert len(want) > 100
+    worst = max(abs(got[k] - want[k]) / want[k] for k in set(got) & set(want))
+    assert worst < 1e-3
+    s.close()
+
+
+def test_peak_list_overflow_is_reported(lib):
+    size, tsamp = 1 << 17, 64e-6
+    trial = make_trials(1, size, size, tsamp=tsamp)[0]
+    s = pb.Search(make_search_params(size, size, tsamp, min_snr=-100.0, max_peaks=1000))
+    s.whiten(torch.from_numpy(trial).cuda())
+    s.reset_peaks()
+    s.accel_batch([0.0])
+    with pytest.raises(pb.PeasoupError, match="max_peaks"):
+        s.fetch_peaks()
+    s.close()
+
+
+# ------------------------------------------------------------------ pipeline-level
+def test_pipeline_vs_oracle_synthetic(lib, oracle):
+    size, nsamps, tsamp = 1 << 17, (1 << 17) + 512, 64e-6
+    ndm = 5
+    trials = make_trials(ndm, nsamps, size, tsamp=tsamp, a_inj=31.4, amp=9.0)
+    dms = np.linspace(0, 40, ndm).astype(np.float32)
+    accs = np.array([0.0, -50.0, -25.0, 25.0, 31.4, 50.0], np.float32)
+    cfg = oracle.SearchConfig(size, tsamp)
+    got, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs)
+    assert done == ndm * len(accs)
+    want = oracle.search(trials, dms, accs, cfg)
+    assert len(want) > 20
+    compare_candidates(got, want, cfg)
+    # ascending DM order, a top-level record first
+    assert np.all(np.diff(got["dm_idx"]) >= 0) and got["is_top"][0] == 1
+
+
+def test_pipeline_acceleration_plan_and_empty(lib, oracle):
+    size, tsamp = 1 << 17, 0.00032
+    trials = make_trials(2, size + 10, size, tsamp=tsamp, a_inj=0.0, p0=0.1, amp=6.0, birdies=False)
+    prm = pipeline_params(size, size + 10, tsamp)
+    prm.acc_start, prm.acc_end, prm.cfreq, prm.foff = -5.0, 5.0, 1475.12, -1.09
+    got, done = pb.pipeline_search(trials, [0.0, 5.0], prm)  # AccelerationPlan -> [0,-5,5]
+    assert done == 6 and set(got["acc"]) <= {0.0, -5.0, 5.0}
+    cfg = oracle.SearchConfig(size, tsamp)
+    want = oracle.search(trials, [0.0, 5.0], np.array([0.0, -5.0, 5.0], np.float32), cfg)
+    compare_candidates(got, want, cfg)
+    got0, done0 = pb.pipeline_search(trials[:0], [], prm)
+    assert len(got0) == 0 and done0 == 0
+
+
+def test_tutorial_fil_matches_golden_candidates(lib, oracle, tutorial_trials):
+    """BASELINE.json configs[0] with the parameters the golden run really used."""
+    trials, ov = tutorial_trials
+    size, tsamp = 1 << 17, 0.00032
+    cfg = oracle.SearchConfig(size, tsamp)
+    got, done = pb.pipeline_search(trials, ov["dm_list"], pipeline_params(size, trials.shape[1], tsamp), accs=ov["acc_list"])
+    assert done == 59 * 3
+    gold = np.concatenate([c["dets"] for c in oracle.parse_candidates_peasoup(os.path.join(GOLDEN, "candidates.peasoup"))])
+    ours = cand_keys(got, cfg.nbins, cfg.bin_width_f)
+    g = cand_keys(gold, cfg.nbins, cfg.bin_width_f)
+    missing = [k for k in g if k not in ours]
+    assert len(gold) == 1032 and len(g) > 900 and not missing, missing[:5]
+    worst = max(abs(ours[k] - g[k]) / g[k] for k in g)
+    assert worst < SNR_TOL, worst
+    # and the full list equals the oracle's, record for record
+    want = oracle.search(trials, ov["dm_list"], ov["acc_list"], cfg)
+    compare_candidates(got, want, cfg)
+    # DM carried through exactly
+    for r in got[:50]:
+        assert r["dm"] == ov["dm_list"][r["dm_idx"]]
+
+
+def ref_search(ref, trials, dms, accs, size, nsamps, tsamp, nharm=4, min_snr=9.0, zapfile=b""):
+    class P(C.Structure):
+        _fields_ = [("size", C.c_uint), ("nsamps", C.c_uint), ("tsamp", C.c_float), ("nharmonics", C.c_int),
+                    ("min_snr", C.c_float), ("min_freq", C.c_float), ("max_freq", C.c_float), ("freq_tol", C.c_float),
+                    ("max_harm", C.c_int), ("zapfile", C.c_char_p)]
+    p = P(size, nsamps, tsamp, nharm, min_snr, 0.1, 1100.0, 1e-4, 16, zapfile)
+    cap = 1 << 20
+    o = {k: np.zeros(cap, t) for k, t in [("dm", "f4"), ("dm_idx", "i4"), ("acc", "f4"), ("nh", "i4"), ("snr", "f4"),
+                                            ("freq", "f4"), ("is_top", "i4")]}
+    dms = np.ascontiguousarray(dms, np.float32)
+    accs = np.ascontiguousarray(accs, np.float32)
+    secs = C.c_double()
+    vp = C.c_void_p
+    ref.ref_worker_search.argtypes = [C.POINTER(P), vp, vp, C.c_int, vp, C.c_int, C.c_long] + [vp] * 7 + [C.POINTER(C.c_double)]
+    n = ref.ref_worker_search(C.byref(p), ptr(trials), ptr(dms), len(dms), ptr(accs), len(accs), cap,
+                              *[ptr(o[k]) for k in ("dm", "dm_idx", "acc", "nh", "snr", "freq", "is_top")], C.byref(secs))
+    assert n >= 0, ref.ref_last_error()
+    out = np.zeros(n, pb.host.CAND_DTYPE)
+    for k in o:
+        out[k] = o[k][:n]
+    return out, secs.value
+
+
+def test_pipeline_vs_reference_cuda_build(lib, oracle, ref, tmp_path):
+    """Same host trials through the unmodified reference (kernels.cu + transform headers + cuFFT,
+    replaying Worker::start) and through ps_pipeline_search: identical candidates."""
+    size, nsamps, tsamp = 1 << 18, (1 << 18) - 5000, 64e-6  # padding path
+    ndm = 4
+    trials = make_trials(ndm, nsamps, size, tsamp=tsamp, a_inj=-20.0, amp=9.0)
+    dms = np.linspace(5, 25, ndm).astype(np.float32)
+    accs = np.array([0.0, -40.0, -20.0, 20.0], np.float32)
+    zf = tmp_path / "zap.txt"
+    zf.write_text(open(os.path.join(GOLDEN, "default_zaplist.txt")).read())
+    zl = np.loadtxt(zf, dtype=np.float32)
+    cfg = oracle.SearchConfig(size, tsamp)
+    want, _ = ref_search(ref, trials, dms, accs, size, nsamps, tsamp, zapfile=str(zf).encode())
+    got, _ = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs, zap=(zl[:, 0], zl[:, 1]))
+    assert len(want) > 10
+    compare_candidates(got, want, cfg)
+
+
+def test_tutorial_vs_reference_cuda_build(lib, oracle, ref, tutorial_trials):
+    trials, ov = tutorial_trials
+    size, tsamp = 1 << 17, 0.00032
+    cfg = oracle.SearchConfig(size, tsamp)
+    want, _ = ref_search(ref, trials, ov["dm_list"], ov["acc_list"], size, trials.shape[1], tsamp)
+    got, _ = pb.pipeline_search(trials, ov["dm_list"], pipeline_params(size, trials.shape[1], tsamp), accs=ov["acc_list"])
+    compare_candidates(got, want, cfg)
+
+
+# ------------------------------------------------------------------ full size (BASELINE configs[1])
+def test_full_size_injected_pulsar_properties(lib, oracle):
+    size, tsamp = 1 << 23, 64e-6
+    nsamps = size + 4096
+    a_inj, p0 = 31.4, 7.5e-3
+    trials = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=a_inj, p0=p0, amp=3.0, seed=7)
+    accs = np.arange(-50, 51, 10, dtype=np.float32)
+    accs = np.sort(np.append(accs, np.float32(a_inj)))
+    zl = np.loadtxt(os.path.join(GOLDEN, "default_zaplist.txt"), dtype=np.float32)
+    got, done = pb.pipeline_search(trials, [42.0], pipeline_params(size, nsamps, tsamp), accs=accs, zap=(zl[:, 0], zl[:, 1]))
+    assert done == len(accs)
+    top = got[got["is_top"] == 1]
+    best = top[np.argmax(top["snr"])]
+    # the strongest candidate is the injected pulsar: at the injected acceleration, at a harmonic
+    # of 1/p0 (a 5 % duty pulse train peaks in a summed spectrum), well above threshold
+    assert best["acc"] == np.float32(a_inj), best
+    ratio = best["freq"] * p0
+    assert abs(ratio - round(ratio)) < 2e-3 or abs(1 / ratio - round(1 / ratio)) < 2e-3, best
+    assert best["snr"] > 30
+    # zapped birdies (50/100 Hz) produce no candidates
+    assert not np.any((np.abs(got["freq"] - 50.0) < 0.05) | (np.abs(got["freq"] - 100.0) < 0.05))
+    # the acceleration distiller keeps the neighbouring-acceleration detections as associates
+    assert (got["is_top"] == 0).sum() > 0
