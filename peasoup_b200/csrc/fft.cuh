@@ -165,10 +165,10 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
 }
 
 // ------------------------------------------------------------------ host-side launchers
+// opt in to > 48 KB dynamic shared memory once per (kernel instantiation, device); `done` must be
+// a static of the CALLING template (one per kernel), not of a helper keyed on the pointer type
 template <class K>
-inline int configure_smem(K kernel, size_t bytes, int device) {
-  // opt in to > 48 KB dynamic shared memory once per (kernel instantiation, device)
-  static bool done[64] = {};
+inline int configure_smem(K kernel, size_t bytes, int device, bool* done) {
   if (!done[device & 63]) {
     PS_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes),
             "cudaFuncSetAttribute");
@@ -183,7 +183,8 @@ template <int R3, bool INV, class Loader>
 inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass1_kernel<R3, INV, Loader>;
-  int rc = configure_smem(k, C::SMEM_BYTES, p->device);
+  static bool done[64] = {};
+  int rc = configure_smem(k, C::SMEM_BYTES, p->device, done);
   if (rc) return rc;
   k<<<fft_grid(p->n2 / C::F), C::THREADS, C::SMEM_BYTES, st>>>(ld, p->Yt, p->tables(), p->n1, p->n2);
   PS_LAUNCHED("fft_pass1_kernel");
@@ -194,7 +195,8 @@ template <int R3, bool INV, class Storer>
 inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass2_kernel<R3, INV, Storer>;
-  int rc = configure_smem(k, C::SMEM_BYTES, p->device);
+  static bool done[64] = {};
+  int rc = configure_smem(k, C::SMEM_BYTES, p->device, done);
   if (rc) return rc;
   k<<<fft_grid(p->n1 / C::F), C::THREADS, C::SMEM_BYTES, st>>>(p->Yt, stor, p->tables(), p->n1, p->n2);
   PS_LAUNCHED("fft_pass2_kernel");
