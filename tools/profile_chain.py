@@ -1,0 +1,17 @@
+"""Small driver for ncu: one DM trial whitened + a few acceleration trials at the bench size."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import peasoup_b200 as pb
+from peasoup_b200.host import make_search_params
+import bench
+
+n_acc = int(sys.argv[1]) if len(sys.argv) > 1 else 6
+torch.cuda.set_device(0)
+d = bench.synth_trials(1, torch.device("cuda:0"), 0)
+s = pb.Search(make_search_params(bench.SIZE, bench.NSAMPS, bench.TSAMP, bench.NFOLDS, 9.0))
+s.set_zaplist(bench.ZAP_F, bench.ZAP_W)
+for rep in range(2):
+    s.whiten(d[0]); s.reset_peaks(); s.accel_batch(bench.ACCS[:n_acc])
+    torch.cuda.synchronize()
+print("peaks", len(s.fetch_peaks()))
