@@ -79,6 +79,29 @@ int ps_linear_stretch(const float* d_in, size_t in_count, float* d_out, size_t o
  * floats. */
 int ps_running_median(const float* d_pspec, unsigned nbins, double bin_width, float boundary_5_freq,
                       float boundary_25_freq, float* d_median, float* d_work, void* stream);
+/* ps_running_median without any allocation and without a work buffer (no counterpart in the
+ * reference; added for this library's users).
+ *
+ * For callers that must not allocate device memory and have no spare buffer to lend: a
+ * real-time acquisition loop where a cudaMalloc would stall every stream of the device, a
+ * plugin running under a host that owns the whole device-memory budget, or code that runs
+ * while other work on the device must not be disturbed.  The three median levels are kept in
+ * an array built into the library (about 4 MiB per GPU, held from library load to exit), so
+ * the call issues only kernel launches: no cudaMalloc, cudaFree or allocating library routine.
+ *
+ *  - nbins above PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS (a 2^23-point search) is rejected with
+ *    PS_EINVAL and a message naming the limit;
+ *  - the first call on each device looks up the array's device address (one
+ *    cudaGetSymbolAddress, with that device current); make that first call before any stream
+ *    capture begins;
+ *  - all calls on a device share the one array: calls whose kernels may overlap on the GPU
+ *    (different streams without ordering between them) race -- serialise them.  Nothing has to
+ *    be cleared between calls: every level is rewritten before it is read;
+ *  - results are identical to ps_running_median on the same input. */
+#define PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS 4194305u
+int ps_running_median_noalloc(const float* d_pspec, unsigned nbins, double bin_width,
+                              float boundary_5_freq, float boundary_25_freq, float* d_median,
+                              void* stream);
 /* device_divide_c_by_f, kernels.h:262 / kernels.cu:1013-1034. */
 int ps_divide_c_by_f(ps_complex* d_c, const float* d_f, unsigned nbins, void* stream);
 /* device_zap_birdies, kernels.h:268 / kernels.cu:1036-1069 (width is a half-width). */

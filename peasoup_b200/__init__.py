@@ -46,7 +46,7 @@ SYMBOLS = [
     "ps_last_error", "ps_version", "ps_resampleII", "ps_resample", "ps_resample_index_map",
     "ps_form_power_series", "ps_normalise", "ps_harmonic_sum", "ps_peak_workspace_create",
     "ps_peak_workspace_destroy", "ps_find_peaks", "ps_median_scrunch5", "ps_linear_stretch",
-    "ps_running_median", "ps_divide_c_by_f", "ps_zap_birdies", "ps_rms", "ps_mean", "ps_fill",
+    "ps_running_median", "ps_running_median_noalloc", "ps_divide_c_by_f", "ps_zap_birdies", "ps_rms", "ps_mean", "ps_fill",
     "ps_convert_u8_f32", "ps_fft_plan_create", "ps_fft_plan_destroy", "ps_fft_r2c", "ps_fft_c2r",
     "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
     "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks",
@@ -84,6 +84,7 @@ def load() -> C.CDLL:
         "ps_find_peaks": [i, i, vp, f, vp, vp, sz, vp, vp],
         "ps_median_scrunch5": [vp, sz, vp, vp], "ps_linear_stretch": [vp, sz, vp, sz, vp],
         "ps_running_median": [vp, u, d, f, f, vp, vp, vp],
+        "ps_running_median_noalloc": [vp, u, d, f, f, vp, vp],
         "ps_divide_c_by_f": [vp, vp, u, vp], "ps_zap_birdies": [vp, vp, vp, f, u, u, vp],
         "ps_rms": [vp, i, i, C.POINTER(f)], "ps_mean": [vp, i, i, C.POINTER(f)], "ps_fill": [vp, vp, f, vp],
         "ps_convert_u8_f32": [vp, vp, u, vp],

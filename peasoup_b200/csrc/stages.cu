@@ -430,6 +430,52 @@ int ps_running_median(const float* d_pspec, unsigned nbins, double bin_width, fl
   return launch_running_median(d_pspec, nbins, bin_width, b5, b25, d_median, d_work, S(stream));
 }
 
+// ---- allocation-free variant of ps_running_median -------------------------------------
+// Scratch for the three median levels lives in this file-scope device array instead of a
+// caller-supplied buffer.  PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS bins (a 2^23-point search) need
+// nbins/5 + nbins/25 + nbins/125 + 3 floats: about 4 MiB, resident on every GPU that loads the
+// library until the process exits.
+namespace ps {
+constexpr size_t kNoAllocScratchWords = PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS / 5 + PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS / 25 +
+                                        PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS / 125 + 8;
+static __device__ __align__(256) float g_noalloc_median_scratch[kNoAllocScratchWords];
+
+// In host code `g_noalloc_median_scratch` is only a handle for the runtime, not an address a
+// kernel may dereference; the real device address is looked up once per device (with that
+// device current) and cached.
+static std::mutex g_noalloc_mu;
+static float* g_noalloc_ptr[64] = {};
+
+static int noalloc_scratch(float** out) {
+  int dev = 0;
+  PS_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
+  if (dev < 0 || dev >= 64) return invalid("ps_running_median_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    float* p = nullptr;
+    PS_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_median_scratch), "cudaGetSymbolAddress(median scratch)");
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return PS_OK;
+}
+}  // namespace ps
+
+int ps_running_median_noalloc(const float* d_pspec, unsigned nbins, double bin_width, float b5, float b25, float* d_median,
+                              void* stream) {
+  if (nbins > PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS) {
+    set_error("ps_running_median_noalloc: nbins = " + std::to_string(nbins) + " exceeds the built-in scratch (max " +
+              std::to_string((unsigned)PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS) +
+              " bins); use ps_running_median with a caller-provided work buffer");
+    return PS_EINVAL;
+  }
+  float* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  // every level is fully rewritten before it is read, so nothing has to be cleared between calls
+  return launch_running_median(d_pspec, nbins, bin_width, b5, b25, d_median, scratch, S(stream));
+}
+
 int ps_divide_c_by_f(ps_complex* d_c, const float* d_f, unsigned nbins, void* stream) {
   if (!nbins) return PS_OK;
   divide_c_by_f_kernel<<<ew_grid(nbins, 256, 4), 256, 0, S(stream)>>>((float2*)d_c, d_f, nbins);
