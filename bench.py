@@ -269,6 +269,8 @@ def main():
     ms_e2e, done_e2e, _ = timed(h_trials, args.steps)
     h1, d1 = C.c_ulonglong(), C.c_ulonglong()
     lib.ps_transfer_bytes(C.byref(h1), C.byref(d1))
+    prof = (C.c_double * 4)()
+    lib.ps_pipeline_profile(prof)
     clocks = sampler.stop()
 
     # roofline: the acceleration-trial kernel chain alone, CUDA events on its own stream
@@ -306,6 +308,8 @@ def main():
                          "kernel": "acceleration-trial chain: fft_pass1(resample gather) + fft_pass2 + spectrum + harmonic_peaks",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_TRIAL, "ms_per_launch": chain_ms},
             "candidates_last_step": int(len(merged)) if merged is not None else None,
+            "host_profile_last_step": {"submit_s": prof[0], "wait_device_s": prof[1], "host_distill_s": prof[2],
+                                       "raw_peaks": int(prof[3])},
         }
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline()

@@ -206,6 +206,11 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
                         const float* h_zap_freqs, const float* h_zap_widths, int nzap, int device0,
                         int nworkers, ps_candidate* out, long max_out, unsigned long long* trials_done);
 
+/* Diagnostics of the last ps_pipeline_search call of this process, summed over workers:
+ * seconds spent queueing device work, waiting for the device, and in host-side clustering +
+ * distillation, then the number of raw above-threshold bins fetched. */
+void ps_pipeline_profile(double* out4);
+
 /* AccelerationPlan::generate_accel_list (utils.hpp:168-192).  Returns the list length. */
 int ps_accel_plan_generate(float acc_lo, float acc_hi, float tol, float pulse_width, unsigned nsamps,
                            float tsamp, float cfreq, float bw, float dm, float* out, int max_out);

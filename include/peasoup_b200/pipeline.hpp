@@ -10,6 +10,7 @@
 // buffering), and the host-side clustering/distillation of trial i overlaps the device work of
 // trial i+1.  Candidate output is identical in content and order to the staged path.
 #pragma once
+#include <chrono>
 #include <mutex>
 #include <thread>
 #include "transforms.hpp"
@@ -70,6 +71,10 @@ class Worker {  // pipeline_multi.cu:83-254
  public:
   CandidateCollection dm_trial_cands;
   unsigned long long trials_done = 0;  // DM x acceleration trials searched
+  // wall-clock split of start(): queueing device work, waiting for the device, host-side
+  // clustering + distillation (diagnostics for bench.py)
+  double t_submit = 0, t_wait = 0, t_host = 0;
+  unsigned long long raw_peaks = 0;
 
   Worker(DispersionTrials<unsigned char>& trials, DMDispenser& manager, AccelerationPlan& acc_plan, SearchArgs& args,
          unsigned int size, int device, const std::vector<float>* fixed_accs = 0, int dm_idx_offset = 0)
@@ -127,7 +132,11 @@ class Worker {  // pipeline_multi.cu:83-254
     std::vector<int> idxs, peakidxs;
     std::vector<float> snrs, peaksnrs, peakfreqs;
 
+    typedef std::chrono::steady_clock clk;
+    auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+
     auto submit = [&](Slot& s) -> bool {
+      clk::time_point t0 = clk::now();
       s.ii = manager.get_dm_trial_idx();
       if (s.ii == -1) return false;
       DedispersedTimeSeries<unsigned char> tim;
@@ -145,12 +154,17 @@ class Worker {  // pipeline_multi.cu:83-254
       ErrorChecker::check(ps_search_reset_peaks(s.search, s.stream));
       ErrorChecker::check(ps_search_whiten(s.search, s.d_trial, 0, 0, s.stream));
       ErrorChecker::check(ps_search_accel_batch(s.search, &s.acc_list[0], (int)s.acc_list.size(), 0, s.stream));
+      t_submit += secs(t0, clk::now());
       return true;
     };
 
     auto finish = [&](Slot& s) {
+      clk::time_point t0 = clk::now();
       long n = ps_search_fetch_peaks(s.search, &s.peaks[0], s.peaks.size(), s.stream);
       ErrorChecker::check((int)std::min<long>(n, 0));
+      clk::time_point t1 = clk::now();
+      t_wait += secs(t0, t1);
+      raw_peaks += (unsigned long long)n;
       CandidateCollection accel_trial_cands;
       long pos = 0;
       for (int jj = 0; jj < (int)s.acc_list.size(); jj++) {
@@ -174,6 +188,7 @@ class Worker {  // pipeline_multi.cu:83-254
       }
       dm_trial_cands.append(acc_still.distill(accel_trial_cands.cands));
       trials_done += s.acc_list.size();
+      t_host += secs(t1, clk::now());
     };
 
     int cur = 0;

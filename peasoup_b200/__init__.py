@@ -51,7 +51,7 @@ SYMBOLS = [
     "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
     "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks",
     "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
-    "ps_transfer_bytes", "ps_pipeline_search",
+    "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile",
     "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
 ]
 
@@ -109,6 +109,8 @@ def load() -> C.CDLL:
     lib.ps_count_transfer.restype = None
     lib.ps_transfer_bytes.argtypes = [C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
     lib.ps_transfer_bytes.restype = None
+    lib.ps_pipeline_profile.argtypes = [C.POINTER(C.c_double)]
+    lib.ps_pipeline_profile.restype = None
     lib.ps_search_fetch_peaks.restype = C.c_long
     lib.ps_pipeline_search.restype = C.c_long
     lib.ps_distill.restype = C.c_long

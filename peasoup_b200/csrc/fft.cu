@@ -57,12 +57,14 @@ static std::vector<cf> roots(unsigned count, unsigned step, unsigned period) {
   return v;
 }
 
-int plan_create(unsigned n, ps_fft_plan_t** out) {
+int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch) {
+  if (max_batch < 1 || max_batch > kMaxBatch) return invalid("plan_create: bad batch");
   if (n < (1u << 17) || n > (1u << 25) || (n & (n - 1)))
     return invalid("ps_fft_plan_create: n must be a power of two with 2^17 <= n <= 2^25");
   ps_fft_plan_t* p = new ps_fft_plan_t();
   p->n = n;
   p->M = n / 2;
+  p->max_batch = max_batch;
   if (pick_split(p->M, &p->n1, &p->n2)) {
     delete p;
     return invalid("ps_fft_plan_create: unsupported length");
@@ -76,17 +78,22 @@ int plan_create(unsigned n, ps_fft_plan_t** out) {
   }
   unsigned na = p->M / 4096 ? p->M / 4096 : 1;
   std::vector<cf> w = roots(4096, 1, 4096), ta = roots(na, 4096, p->M), tb = roots(4096, 1, p->M);
-  p->W4096 = p->TA = p->TB = p->Yt = p->Z = nullptr;
+  std::vector<cf> tc = roots(na + 1, 4096, 2 * p->M), td = roots(4096, 1, 2 * p->M);
+  p->W4096 = p->TA = p->TB = p->Yt = p->Z = p->TC = p->TD = nullptr;
   e = cudaMalloc(&p->W4096, sizeof(cf) * 4096);
   if (e == cudaSuccess) e = cudaMalloc(&p->TA, sizeof(cf) * na);
   if (e == cudaSuccess) e = cudaMalloc(&p->TB, sizeof(cf) * 4096);
-  if (e == cudaSuccess) e = cudaMalloc(&p->Yt, sizeof(cf) * (size_t)p->M);
-  if (e == cudaSuccess) e = cudaMalloc(&p->Z, sizeof(cf) * (size_t)p->M);
+  if (e == cudaSuccess) e = cudaMalloc(&p->Yt, sizeof(cf) * (size_t)p->M * max_batch);
+  if (e == cudaSuccess) e = cudaMalloc(&p->Z, sizeof(cf) * (size_t)p->M * max_batch);
+  if (e == cudaSuccess) e = cudaMalloc(&p->TC, sizeof(cf) * (na + 1));
+  if (e == cudaSuccess) e = cudaMalloc(&p->TD, sizeof(cf) * 4096);
+  if (e == cudaSuccess) e = cudaMemcpy(p->TC, tc.data(), sizeof(cf) * (na + 1), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(p->TD, td.data(), sizeof(cf) * 4096, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(p->W4096, w.data(), sizeof(cf) * 4096, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(p->TA, ta.data(), sizeof(cf) * na, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(p->TB, tb.data(), sizeof(cf) * 4096, cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
-    cudaFree(p->W4096); cudaFree(p->TA); cudaFree(p->TB); cudaFree(p->Yt); cudaFree(p->Z);
+    cudaFree(p->W4096); cudaFree(p->TA); cudaFree(p->TB); cudaFree(p->Yt); cudaFree(p->Z); cudaFree(p->TC); cudaFree(p->TD);
     delete p;
     return cuda_fail(e, "Error from device_malloc");
   }
@@ -96,7 +103,7 @@ int plan_create(unsigned n, ps_fft_plan_t** out) {
 
 void plan_destroy(ps_fft_plan_t* p) {
   if (!p) return;
-  cudaFree(p->W4096); cudaFree(p->TA); cudaFree(p->TB); cudaFree(p->Yt); cudaFree(p->Z);
+  cudaFree(p->W4096); cudaFree(p->TA); cudaFree(p->TB); cudaFree(p->Yt); cudaFree(p->Z); cudaFree(p->TC); cudaFree(p->TD);
   delete p;
 }
 
@@ -112,7 +119,7 @@ extern "C" {
 
 int ps_fft_plan_create(unsigned n, ps_fft_plan** out) {
   ps_fft_plan_t* p = nullptr;
-  int rc = plan_create(n, &p);
+  int rc = plan_create(n, &p, 1);
   if (rc) return rc;
   *out = reinterpret_cast<ps_fft_plan*>(p);
   return PS_OK;
@@ -124,10 +131,10 @@ int ps_fft_r2c(ps_fft_plan* plan, const float* d_in, ps_complex* d_out, void* st
   if (!plan) return invalid("ps_fft_r2c: null plan");
   const ps_fft_plan_t* p = reinterpret_cast<ps_fft_plan_t*>(plan);
   cudaStream_t st = S(stream);
-  LoadPackedReal ld{reinterpret_cast<const float2*>(d_in), p->n2, 0};
+  LoadPackedReal ld{reinterpret_cast<const float2*>(d_in), 0, 0, 0, nullptr};
   int rc = launch_pass1<false>(p, ld, st);
   if (rc) return rc;
-  StoreNatural sn{reinterpret_cast<float2*>(p->Z), p->n1, 0};
+  StoreNatural sn{reinterpret_cast<float2*>(p->Z), 0, 0, 0, nullptr};
   rc = launch_pass2<false>(p, sn, st);
   if (rc) return rc;
   return launch_r2c_post(p, p->Z, reinterpret_cast<float2*>(d_out), st);
@@ -137,10 +144,10 @@ int ps_fft_c2r(ps_fft_plan* plan, const ps_complex* d_in, float* d_out, void* st
   if (!plan) return invalid("ps_fft_c2r: null plan");
   const ps_fft_plan_t* p = reinterpret_cast<ps_fft_plan_t*>(plan);
   cudaStream_t st = S(stream);
-  LoadC2RPre ld{reinterpret_cast<const float2*>(d_in), p->M, p->n2, 0};
+  LoadC2RPre ld{reinterpret_cast<const float2*>(d_in), p->M, 0, 0};
   int rc = launch_pass1<true>(p, ld, st);
   if (rc) return rc;
-  StoreNatural sn{reinterpret_cast<float2*>(d_out), p->n1, 0};
+  StoreNatural sn{reinterpret_cast<float2*>(d_out), 0, 0, 0, nullptr};
   return launch_pass2<true>(p, sn, st);
 }
 

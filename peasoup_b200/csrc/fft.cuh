@@ -32,8 +32,11 @@ struct ps_fft_plan_t {
   cf* W4096;
   cf* TA;
   cf* TB;
-  cf* Yt;  // M complex: transposed intermediate between the passes
-  cf* Z;   // M complex: packed-complex spectrum before the real post-process
+  int max_batch;  // Yt and Z hold max_batch transforms
+  cf* Yt;  // max_batch x M complex: transposed intermediate between the passes
+  cf* Z;   // max_batch x M complex: packed-complex spectrum before the real post-process
+  cf* TC;  // exp(-i pi 4096 q / M), q <= M/4096   (real-FFT split twiddle W_N^k, N = 2M)
+  cf* TD;  // exp(-i pi q / M), q < 4096
   FftTables tables() const { return FftTables{W4096, TA, TB}; }
 };
 
@@ -42,34 +45,111 @@ __device__ __forceinline__ cf twiddle_M(const FftTables& t, unsigned p) {
   return psfft::cmul(psfft::ldg_cf(&t.TA[p >> 12]), psfft::ldg_cf(&t.TB[p & 4095u]));
 }
 
+// cp.async (LDGSTS): global -> shared without staging through registers
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // ------------------------------------------------------------------ pass-1 loaders
+// Loaders with kAsync = true also provide prefetch(f, idx, dst): an asynchronous copy of the
+// element into the thread's own staging slot, so the next tile's operands are in flight while
+// the current tile is being transformed.
+// Every loader/storer has begin(b, first, n): b = batch item (independent transform sharing the
+// plan), first = first column (pass 1) / row (pass 2) of the CTA tile, n = n2 (pass 1) / n1 (pass 2).
 // complex element e = idx*n2 + c0 + f of the packed series
+constexpr int kMaxBatch = 8;
+
 struct LoadPackedReal {  // z[e] = (x[2e], x[2e+1])
+  static constexpr bool kAsync = true;
+  __device__ __forceinline__ void prefetch(int f, int idx, cf* dst) const {
+    cp_async8(dst, &xb[(size_t)idx * n2 + c0 + f]);
+  }
   const float2* x;
+  size_t item_stride;  // in float2
   int n2, c0;
+  const float2* xb;
+  __device__ __forceinline__ void begin(int b, int first, int n) {
+    xb = x + (size_t)b * item_stride;
+    c0 = first;
+    n2 = n;
+  }
   __device__ __forceinline__ cf operator()(int f, int idx) const {
-    float2 v = __ldg(&x[(size_t)idx * n2 + c0 + f]);
+    float2 v = __ldg(&xb[(size_t)idx * n2 + c0 + f]);
     return psfft::mk(v.x, v.y);
   }
 };
 
-struct LoadResampled {  // z[e] = (x[map(2e)], x[map(2e+1)])   (kernels.cu:335-346 fused)
+struct AccelFacts {
+  double v[kMaxBatch];
+};
+
+// z[e] = (x[map(2e)], x[map(2e+1)]): the resampling gather of kernels.cu:335-346 fused into the
+// FFT load.  The read index is bit-identical to resample_kernelII: a float32 evaluation of the
+// shift i*af*(i-N) decides it whenever it lies safely away from a rounding boundary (the shift is
+// then rn(shift32)); otherwise the reference's FP64 expression is evaluated.
+struct LoadResampled {
+  static constexpr bool kAsync = true;
   const float* x;
-  double af, size;
+  AccelFacts afs;
+  double size;
+  float max_shift;  // host bound on |i*af*(i-N)| over the series, all batch items
+  float max_step;   // host bound on |shift(i+1) - shift(i)|
+  double af;
+  float af32, fsize, thr;
   int n2, c0;
+  __device__ __forceinline__ void begin(int b, int first, int n) {
+    af = afs.v[b];
+    af32 = (float)af;
+    fsize = (float)size;
+    // float32 evaluation error <= 4e-7*|shift|; a shift estimate this far from a half-integer fixes
+    // the rounding of both samples of a pair
+    thr = 0.5f - (1e-3f + 4e-6f * max_shift + max_step);
+    c0 = first;
+    n2 = n;
+  }
+  __device__ __forceinline__ void indices(int f, int idx, unsigned* i0, unsigned* i1) const {
+    const unsigned i = 2u * ((unsigned)idx * (unsigned)n2 + (unsigned)(c0 + f));
+    const float fi = (float)i;                          // exact below 2^24
+    const float g = (fi * (fi - fsize)) * af32;         // shift estimate
+    const float tm = g + 12582912.f;                    // 1.5*2^23: rounds g to an integer (ties to even)
+    const float r = tm - 12582912.f;
+    if (fabsf(g - r) < thr && i < (1u << 24)) {
+      *i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
+      *i1 = *i0 + 1;
+    } else {  // the reference's FP64 expression (kernels.cu:314-317)
+      *i0 = (unsigned)resample_index_II(af, size, i);
+      *i1 = (unsigned)resample_index_II(af, size, i + 1);
+    }
+  }
   __device__ __forceinline__ cf operator()(int f, int idx) const {
-    unsigned long long i = 2ull * ((unsigned long long)idx * n2 + c0 + f);
-    float a = __ldg(&x[resample_index_II(af, size, i)]);
-    float b = __ldg(&x[resample_index_II(af, size, i + 1)]);
-    return psfft::mk(a, b);
+    unsigned i0, i1;
+    indices(f, idx, &i0, &i1);
+    return psfft::mk(__ldg(&x[i0]), __ldg(&x[i1]));
+  }
+  __device__ __forceinline__ void prefetch(int f, int idx, cf* dst) const {
+    unsigned i0, i1;
+    indices(f, idx, &i0, &i1);
+    cp_async4(&dst->x, &x[i0]);
+    cp_async4(&dst->y, &x[i1]);
   }
 };
 
 struct LoadU8Padded {  // timeseries.hpp:335-344 + pipeline_multi.cu:160-163 fused
+  static constexpr bool kAsync = false;
+  __device__ __forceinline__ void prefetch(int, int, cf*) const {}
   const unsigned char* b;
   const float* pad;  // device scalar: mean of the first nsamps samples
   unsigned nsamps;   // valid samples (<= size)
   int n2, c0;
+  __device__ __forceinline__ void begin(int, int first, int n) {
+    c0 = first;
+    n2 = n;
+  }
   __device__ __forceinline__ cf operator()(int f, int idx) const {
     size_t i = 2 * ((size_t)idx * n2 + c0 + f);
     float p = 0.f;
@@ -82,9 +162,15 @@ struct LoadU8Padded {  // timeseries.hpp:335-344 + pipeline_multi.cu:160-163 fus
 
 // C2R pre-process: Z'[k] = (X[k] + conj X[M-k]) + i (X[k] - conj X[M-k]) W_N^-k
 struct LoadC2RPre {
+  static constexpr bool kAsync = false;
+  __device__ __forceinline__ void prefetch(int, int, cf*) const {}
   const float2* X;  // M+1 bins
   unsigned M;
   int n2, c0;
+  __device__ __forceinline__ void begin(int, int first, int n) {
+    c0 = first;
+    n2 = n;
+  }
   __device__ __forceinline__ cf operator()(int f, int idx) const {
     unsigned k = (unsigned)idx * n2 + c0 + f;
     float2 xa = __ldg(&X[k]);
@@ -103,15 +189,28 @@ struct StorePass1 {
   cf* Yt;
   FftTables t;
   int n1, c0;
-  __device__ __forceinline__ void operator()(int f, int k, cf v) const {
-    unsigned j2 = (unsigned)(c0 + f);
-    cf w = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k));
-    v = psfft::cmul(v, w);
-    reinterpret_cast<float2*>(Yt)[(size_t)j2 * n1 + k] = make_float2(v.x, v.y);
+  // outputs k = k0 + stride*j of column j2: multiply by W_M^(j2*k) = base * step^j (two
+  // interleaved chains, <= R/2 roundings deep) and store the column run
+  template <int R>
+  __device__ __forceinline__ void store(int f, int k0, int stride, const cf* v) const {
+    const unsigned j2 = (unsigned)(c0 + f);
+    const cf base = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k0));
+    cf pw[R > 1 ? R : 2];
+    psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride)));
+    float2* col = reinterpret_cast<float2*>(Yt) + (size_t)j2 * n1 + k0;
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+      cf o = psfft::cmul(v[j], pw[j]);
+      col[stride * j] = make_float2(o.x, o.y);
+    }
   }
 };
 
 struct LoadPass2 {
+  static constexpr bool kAsync = true;
+  __device__ __forceinline__ void prefetch(int f, int idx, cf* dst) const {
+    cp_async8(dst, &Yt[(size_t)idx * n1 + r0 + f]);
+  }
   const cf* Yt;
   int n1, r0;
   __device__ __forceinline__ cf operator()(int f, int idx) const {
@@ -122,44 +221,88 @@ struct LoadPass2 {
 
 struct StoreNatural {  // out[k1 + n1*k2]
   float2* out;
+  size_t item_stride;  // in float2
   int n1, r0;
-  __device__ __forceinline__ void operator()(int f, int k, cf v) const {
-    out[(size_t)k * n1 + r0 + f] = make_float2(v.x, v.y);
+  float2* ob;
+  __device__ __forceinline__ void begin(int b, int first, int n) {
+    ob = out + (size_t)b * item_stride;
+    r0 = first;
+    n1 = n;
+  }
+  template <int R>
+  __device__ __forceinline__ void store(int f, int k0, int stride, const cf* v) const {
+    float2* o = ob + (size_t)k0 * n1 + r0 + f;
+    const size_t step = (size_t)stride * n1;
+#pragma unroll
+    for (int j = 0; j < R; j++) o[step * j] = make_float2(v[j].x, v[j].y);
   }
 };
 
+// One work item = F transforms of one batch item.  The 16 operands of every thread for the NEXT
+// work item are loaded into registers between phase B and phase C of the current one (phase C
+// is the light radix-R3 stage), so their latency overlaps phase C and the stores.
+template <class C, class Loader>
+__device__ __forceinline__ void load_operands(const Loader& ld, cf* v) {
+  const int t = threadIdx.x, f = t % C::F, u = t / C::F;
+#pragma unroll
+  for (int a = 0; a < 16; a++) v[a] = ld(f, a * C::G + u);
+}
+
+// grid-stride over (batch item, tile); items are independent transforms with their own Yt slice
 template <int R3, bool INV, class Loader>
-__global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader proto, cf* Yt, FftTables t, int n1, int n2) {
+__global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, FftTables t, int n1, int n2, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   extern __shared__ float smem[];
   const int ntiles = n2 / C::F;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    Loader ld = proto;
-    ld.c0 = tile * C::F;
-    ld.n2 = n2;
-    StorePass1<INV> st{Yt, t, n1, tile * C::F};
-    C::phaseA(threadIdx.x, smem, t.W4096, ld);
+  const int nwork = ntiles * nbatch;
+  const size_t M = (size_t)n1 * n2;
+  int work = blockIdx.x;
+  if (work >= nwork) return;
+  cf v[16];
+  ld.begin(work / ntiles, (work % ntiles) * C::F, n2);
+  load_operands<C>(ld, v);
+  for (; work < nwork; work += gridDim.x) {
+    const int b = work / ntiles, tile = work - b * ntiles;
+    StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F};
+    C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
     __syncthreads();
     C::phaseB(threadIdx.x, smem, t.W4096, st);
     __syncthreads();
+    const int next = work + gridDim.x;
+    if (next < nwork) {
+      ld.begin(next / ntiles, (next % ntiles) * C::F, n2);
+      load_operands<C>(ld, v);
+    }
     C::phaseC(threadIdx.x, smem, st);
   }
 }
 
 template <int R3, bool INV, class Storer>
-__global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer proto, FftTables t, int n1, int n2) {
+__global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer st, FftTables t, int n1, int n2, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   extern __shared__ float smem[];
   const int ntiles = n1 / C::F;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    LoadPass2 ld{Yt, n1, tile * C::F};
-    Storer st = proto;
-    st.r0 = tile * C::F;
-    st.n1 = n1;
-    C::phaseA(threadIdx.x, smem, t.W4096, ld);
+  const int nwork = ntiles * nbatch;
+  const size_t M = (size_t)n1 * n2;
+  int work = blockIdx.x;
+  if (work >= nwork) return;
+  cf v[16];
+  {
+    LoadPass2 ld{Yt + (size_t)(work / ntiles) * M, n1, (work % ntiles) * C::F};
+    load_operands<C>(ld, v);
+  }
+  for (; work < nwork; work += gridDim.x) {
+    const int b = work / ntiles, tile = work - b * ntiles;
+    st.begin(b, tile * C::F, n1);
+    C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
     __syncthreads();
     C::phaseB(threadIdx.x, smem, t.W4096, st);
     __syncthreads();
+    const int next = work + gridDim.x;
+    if (next < nwork) {
+      LoadPass2 ld{Yt + (size_t)(next / ntiles) * M, n1, (next % ntiles) * C::F};
+      load_operands<C>(ld, v);
+    }
     C::phaseC(threadIdx.x, smem, st);
   }
 }
@@ -180,25 +323,27 @@ inline int configure_smem(K kernel, size_t bytes, int device, bool* done) {
 inline int fft_grid(int ntiles) { return ntiles < 148 ? ntiles : 148; }
 
 template <int R3, bool INV, class Loader>
-inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st) {
+inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass1_kernel<R3, INV, Loader>;
   static bool done[64] = {};
-  int rc = configure_smem(k, C::SMEM_BYTES, p->device, done);
+  const size_t smem = C::SMEM_BYTES;
+  int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
-  k<<<fft_grid(p->n2 / C::F), C::THREADS, C::SMEM_BYTES, st>>>(ld, p->Yt, p->tables(), p->n1, p->n2);
+  k<<<fft_grid(p->n2 / C::F * nbatch), C::THREADS, smem, st>>>(ld, p->Yt, p->tables(), p->n1, p->n2, nbatch);
   PS_LAUNCHED("fft_pass1_kernel");
   return PS_OK;
 }
 
 template <int R3, bool INV, class Storer>
-inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st) {
+inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass2_kernel<R3, INV, Storer>;
   static bool done[64] = {};
-  int rc = configure_smem(k, C::SMEM_BYTES, p->device, done);
+  const size_t smem = C::SMEM_BYTES;
+  int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
-  k<<<fft_grid(p->n1 / C::F), C::THREADS, C::SMEM_BYTES, st>>>(p->Yt, stor, p->tables(), p->n1, p->n2);
+  k<<<fft_grid(p->n1 / C::F * nbatch), C::THREADS, smem, st>>>(p->Yt, stor, p->tables(), p->n1, p->n2, nbatch);
   PS_LAUNCHED("fft_pass2_kernel");
   return PS_OK;
 }
@@ -214,15 +359,15 @@ inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream
   }
 
 template <bool INV, class Loader>
-inline int launch_pass1(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st) {
-#define PS_CALL1(R) launch_pass1_r<R, INV, Loader>(p, ld, st)
+inline int launch_pass1(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch = 1) {
+#define PS_CALL1(R) launch_pass1_r<R, INV, Loader>(p, ld, st, nbatch)
   PS_DISPATCH_R(p->r1, PS_CALL1)
 #undef PS_CALL1
 }
 
 template <bool INV, class Storer>
-inline int launch_pass2(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st) {
-#define PS_CALL2(R) launch_pass2_r<R, INV, Storer>(p, stor, st)
+inline int launch_pass2(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch = 1) {
+#define PS_CALL2(R) launch_pass2_r<R, INV, Storer>(p, stor, st, nbatch)
   PS_DISPATCH_R(p->r2, PS_CALL2)
 #undef PS_CALL2
 }

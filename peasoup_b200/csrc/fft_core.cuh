@@ -148,87 +148,96 @@ PS_HD void twiddle_powers16(cf* v, cf w1) {
   for (int k = 1; k < 16; k++) v[k] = cmul(v[k], w[k]);
 }
 
+// w[k] = w1^k for k = 1..R-1 as a balanced product tree; w[0] is not touched
+template <int R>
+PS_HD void power_tree(cf* w, cf w1) {
+  w[1] = w1;
+#pragma unroll
+  for (int k = 2; k < R; k++) w[k] = cmul(w[k / 2], w[k - k / 2]);
+}
+
+// w[j] = base * s^j, j < R, as two interleaved chains (even/odd j) of step s^2: R/2 roundings deep
+template <int R>
+PS_HD void chain_powers(cf* w, cf base, cf s1) {
+  w[0] = base;
+  if (R > 1) w[1] = cmul(base, s1);
+  if (R > 2) {
+    const cf s2 = cmul(s1, s1);
+#pragma unroll
+    for (int j = 2; j < R; j++) w[j] = cmul(w[j - 2], s2);
+  }
+}
+
 // One CTA-wide batch of F FFTs of length n = 256*R3.  512 threads; thread t = u*F + f.
+// Shared memory holds complex words (8 bytes): a warp always touches 32 consecutive complex
+// words (256 contiguous bytes, two conflict-free half-warp phases).
+// Storer interface: st.template store<R>(f, k0, stride, v) receives outputs k0 + stride*j, j < R.
 template <int R3, bool INV>
 struct CtaFft {
   static constexpr int F = 32 / R3;
   static constexpr int G = 16 * R3;      // threads per FFT
   static constexpr int N = 256 * R3;     // FFT length
   static constexpr int THREADS = F * G;  // 512
-  static constexpr int E1_WORDS = 16 * G * F;
-  static constexpr int E2_WORDS = (R3 > 1) ? 256 * (R3 + 1) * F : 0;
-  static constexpr int SMEM_WORDS = 2 * (E1_WORDS + E2_WORDS);  // re+im planes
+  static constexpr int E1_WORDS = 16 * G * F;                          // complex words
+  static constexpr int E2_WORDS = (R3 > 1) ? 256 * (R3 + 1) * F : 0;   // complex words
+  static constexpr int SMEM_WORDS = 2 * (E1_WORDS + E2_WORDS);         // float words
   static constexpr size_t SMEM_BYTES = sizeof(float) * SMEM_WORDS;
 
   // W4096[q] = exp(-2*pi*i*q/4096), q in [0,4096)
   template <class Loader>
   PS_HD static void phaseA(int t, float* s, const cf* W4096, const Loader& ld) {
     const int f = t % F, u = t / F;
-    float* e1r = s;
-    float* e1i = s + E1_WORDS;
     cf v[16];
 #pragma unroll
     for (int a = 0; a < 16; a++) v[a] = ld(f, a * G + u);
+    phaseA_regs(t, s, W4096, v);
+  }
+
+  // v[a] = element a*G + u of FFT f, already in registers
+  PS_HD static void phaseA_regs(int t, float* s, const cf* W4096, cf* v) {
+    const int f = t % F, u = t / F;
+    cf* e1 = reinterpret_cast<cf*>(s);
     dft16<INV>(v);
     cf w1 = ldg_cf(&W4096[u * (4096 / N)]);
-    cf wd = dirw<INV>(w1);
-    twiddle_powers16(v, wd);
+    twiddle_powers16(v, dirw<INV>(w1));
 #pragma unroll
-    for (int ka = 0; ka < 16; ka++) {
-      e1r[(ka * G + u) * F + f] = v[ka].x;
-      e1i[(ka * G + u) * F + f] = v[ka].y;
-    }
+    for (int ka = 0; ka < 16; ka++) e1[(ka * G + u) * F + f] = v[ka];
   }
 
   template <class Storer>
   PS_HD static void phaseB(int t, float* s, const cf* W4096, const Storer& st) {
     const int f = t % F, u = t / F;
     const int ka = u / R3, c = u % R3;
-    const float* e1r = s;
-    const float* e1i = s + E1_WORDS;
+    const cf* e1 = reinterpret_cast<const cf*>(s);
     cf v[16];
 #pragma unroll
-    for (int b = 0; b < 16; b++) {
-      int a = (ka * G + b * R3 + c) * F + f;
-      v[b] = mk(e1r[a], e1i[a]);
-    }
+    for (int b = 0; b < 16; b++) v[b] = e1[(ka * G + b * R3 + c) * F + f];
     dft16<INV>(v);
     if (R3 == 1) {
-#pragma unroll
-      for (int kb = 0; kb < 16; kb++) st(f, ka + 16 * kb, v[kb]);
+      st.template store<16>(f, ka, 16, v);
       return;
     }
     cf w1 = ldg_cf(&W4096[c * (256 / R3)]);  // W_(16*R3)^c
     twiddle_powers16(v, dirw<INV>(w1));
-    float* e2r = s + 2 * E1_WORDS;
-    float* e2i = e2r + E2_WORDS;
+    cf* e2 = reinterpret_cast<cf*>(s) + E1_WORDS;
 #pragma unroll
-    for (int kb = 0; kb < 16; kb++) {
-      int a = ((ka + 16 * kb) * (R3 + 1) + c) * F + f;
-      e2r[a] = v[kb].x;
-      e2i[a] = v[kb].y;
-    }
+    for (int kb = 0; kb < 16; kb++) e2[((ka + 16 * kb) * (R3 + 1) + c) * F + f] = v[kb];
   }
 
   template <class Storer>
   PS_HD static void phaseC(int t, const float* s, const Storer& st) {
     if (R3 == 1) return;
     const int f = t % F, u = t / F;
-    const float* e2r = s + 2 * E1_WORDS;
-    const float* e2i = e2r + E2_WORDS;
+    const cf* e2 = reinterpret_cast<const cf*>(s) + E1_WORDS;
     constexpr int RR = (R3 > 1) ? R3 : 2;
 #pragma unroll
     for (int m = 0; m < 16 / RR; m++) {
       const int q = u + G * m;
       cf w[RR];
 #pragma unroll
-      for (int c = 0; c < RR; c++) {
-        int a = (q * (R3 + 1) + c) * F + f;
-        w[c] = mk(e2r[a], e2i[a]);
-      }
+      for (int c = 0; c < RR; c++) w[c] = e2[(q * (R3 + 1) + c) * F + f];
       dftR<RR, INV>(w);
-#pragma unroll
-      for (int kc = 0; kc < RR; kc++) st(f, q + 256 * kc, w[kc]);
+      st.template store<RR>(f, q, 256, w);
     }
   }
 };

@@ -10,6 +10,8 @@ void set_error(const std::string& msg);
 }
 using namespace peasoup_b200;
 
+static double g_prof[4] = {0, 0, 0, 0};  // submit, wait, host seconds; raw peaks (last call, summed over workers)
+
 static long flatten(std::vector<Candidate>& cands, ps_candidate* out, long max_out) {
   long n = 0;
   for (size_t i = 0; i < cands.size(); i++) {
@@ -78,6 +80,13 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
       dm_cands.append(workers[i]->dm_trial_cands.cands);
       done += workers[i]->trials_done;
     }
+    g_prof[0] = g_prof[1] = g_prof[2] = g_prof[3] = 0;
+    for (int i = 0; i < nworkers; i++) {
+      g_prof[0] += workers[i]->t_submit;
+      g_prof[1] += workers[i]->t_wait;
+      g_prof[2] += workers[i]->t_host;
+      g_prof[3] += (double)workers[i]->raw_peaks;
+    }
     for (int i = 0; i < nworkers; i++) delete workers[i];
     for (int i = 0; i < nworkers; i++)
       if (errors[i]) std::rethrow_exception(errors[i]);
@@ -90,6 +99,10 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
     ps::set_error(e.what());
     return PS_ECUDA;
   }
+}
+
+void ps_pipeline_profile(double* out4) {
+  for (int i = 0; i < 4; i++) out4[i] = g_prof[i];
 }
 
 int ps_accel_plan_generate(float acc_lo, float acc_hi, float tol, float pulse_width, unsigned nsamps, float tsamp,

@@ -17,7 +17,8 @@
 
 namespace ps {
 
-int plan_create(unsigned n, ps_fft_plan_t** out);
+int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
+constexpr int kAccelBatch = 2;  // acceleration trials per launch (fills the tail of the 148-SM waves)
 void plan_destroy(ps_fft_plan_t* p);
 
 struct LevelRanges {
@@ -25,83 +26,223 @@ struct LevelRanges {
   int limit[6];
 };
 
+// W_N^k = exp(-i pi k / M) for k in [0, M] from the plan's two-level table
+__device__ __forceinline__ float2 twiddle_N(const cf* __restrict__ TC, const cf* __restrict__ TD, unsigned k) {
+  cf w = psfft::cmul(psfft::ldg_cf(&TC[k >> 12]), psfft::ldg_cf(&TD[k & 4095u]));
+  return make_float2(w.x, w.y);
+}
+
+// X[k] = E + W_N^k O from the packed spectrum (E, O: even/odd-sample transforms)
+__device__ __forceinline__ float2 split_bin(float2 zk, float2 zm, float2 w) {
+  float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);
+  float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x);
+  return make_float2(er + (w.x * orr - w.y * oi), ei + (w.x * oi + w.y * orr));
+}
+
 // Z (packed complex spectrum) -> normalised interbinned amplitude spectrum P[0..M]
 // (r2c split, kernels.cu:231-252 interbin, kernels.cu:469-480 normalise with mean*size,std*size
-// as in pipeline_multi.cu:224).
-__global__ void __launch_bounds__(256) spectrum_kernel(const float2* __restrict__ Z, float* __restrict__ P, unsigned M,
-                                                       const float* __restrict__ stats, float fsize) {
+// as in pipeline_multi.cu:224).  One thread = 4 consecutive bins (+ the left neighbour of the
+// first); blockIdx.y = batch item.  The split twiddle advances by the constant W_N^1 inside a
+// thread; the square root is MUFU.SQRT (<= 1 ulp) and the division a multiplication by 1/sigma
+// (<= 1.5 ulp) -- within 2 ulp of the IEEE results of the staged ps_form_power_series/ps_normalise.
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+__global__ void __launch_bounds__(256) spectrum_kernel(const float2* __restrict__ Zall, float* __restrict__ Pall, unsigned M,
+                                                       size_t pstride, const float* __restrict__ stats, float fsize,
+                                                       const cf* __restrict__ TC, const cf* __restrict__ TD, float2 w1) {
+  const float2* __restrict__ Z = Zall + (size_t)blockIdx.y * M;
+  float* __restrict__ P = Pall + (size_t)blockIdx.y * pstride;
   const float mean = __fmul_rn(stats[0], fsize);
-  const float sigma = __fmul_rn(stats[2], fsize);
-  const unsigned lane = threadIdx.x & 31;
-  const unsigned nb = M + 1;
-  // whole warps iterate together so the shuffles are convergent
-  for (unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < nb; base += gridDim.x * blockDim.x) {
-    unsigned k = base + lane;
-    float2 x = make_float2(0.f, 0.f);
-    if (k < nb) {
-      float2 zk = Z[k == M ? 0 : k];
-      float2 zm = Z[(k == 0 || k == M) ? 0 : M - k];
-      float wr, wi;
-      sincospif((float)k / (float)M, &wi, &wr);
-      float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);
-      float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x);
-      x = make_float2(er + (wr * orr + wi * oi), ei + (wr * oi - wi * orr));
+  const float inv_sigma = __fdiv_rn(1.0f, __fmul_rn(stats[2], fsize));
+  const unsigned ngroups = M / 4;  // bins [0, M) in groups of 4; bin M handled with the last group
+  for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+    const unsigned k0 = 4 * g;
+    const float4 za = *reinterpret_cast<const float4*>(&Z[k0]);           // Z[k0], Z[k0+1]
+    const float4 zb = *reinterpret_cast<const float4*>(&Z[k0 + 2]);       // Z[k0+2], Z[k0+3]
+    const float4 m12 = *reinterpret_cast<const float4*>(&Z[M - k0 - 2]);  // Z[M-k0-2], Z[M-k0-1]
+    const float2 m3 = Z[M - k0 - 3];
+    const float2 m0 = Z[k0 == 0 ? 0 : M - k0];  // Z[M] == Z[0]
+    const float2 zk[4] = {make_float2(za.x, za.y), make_float2(za.z, za.w), make_float2(zb.x, zb.y), make_float2(zb.z, zb.w)};
+    const float2 zm[4] = {m0, make_float2(m12.z, m12.w), make_float2(m12.x, m12.y), m3};
+    float2 w = twiddle_N(TC, TD, k0);
+    float2 left = make_float2(0.f, 0.f);  // left neighbour of bin 0 is zero (kernels.cu:236-241)
+    if (k0) {
+      // W_N^(k0-1) = W_N^k0 * conj(W_N^1)
+      float2 wl = make_float2(w.x * w1.x + w.y * w1.y, w.y * w1.x - w.x * w1.y);
+      left = split_bin(Z[k0 - 1], Z[M - k0 + 1], wl);
     }
-    float lx = __shfl_up_sync(0xffffffffu, x.x, 1);
-    float ly = __shfl_up_sync(0xffffffffu, x.y, 1);
-    if (lane == 0) {
-      lx = 0.f;
-      ly = 0.f;
-      if (k > 0 && k < nb) {
-        unsigned kl = k - 1;
-        float2 zk = Z[kl];
-        float2 zm = Z[kl == 0 ? 0 : M - kl];
-        float wr, wi;
-        sincospif((float)kl / (float)M, &wi, &wr);
-        float er = 0.5f * (zk.x + zm.x), ei = 0.5f * (zk.y - zm.y);
-        float orr = 0.5f * (zk.y + zm.y), oi = -0.5f * (zk.x - zm.x);
-        lx = er + (wr * orr + wi * oi);
-        ly = ei + (wr * oi - wi * orr);
-      }
+    float out[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const float2 x = split_bin(zk[j], zm[j], w);
+      const float ampsq = x.x * x.x + x.y * x.y;
+      const float dr = x.x - left.x, di = x.y - left.y;
+      const float diff = 0.5f * (dr * dr + di * di);
+      out[j] = (sqrt_approx(fmaxf(ampsq, diff)) - mean) * inv_sigma;
+      left = x;
+      w = make_float2(w.x * w1.x - w.y * w1.y, w.x * w1.y + w.y * w1.x);
     }
-    if (k < nb) P[k] = normalise_value(interbin_amplitude(x.x, x.y, lx, ly), mean, sigma);
+    *reinterpret_cast<float4*>(&P[k0]) = make_float4(out[0], out[1], out[2], out[3]);
+    if (k0 + 4 == M) {  // Nyquist bin: X[M] = Re Z0 - Im Z0
+      const float2 z0 = Z[0];
+      const float xr = z0.x - z0.y;
+      const float dr = xr - left.x, di = -left.y;
+      P[M] = (sqrt_approx(fmaxf(xr * xr, 0.5f * (dr * dr + di * di))) - mean) * inv_sigma;
+    }
   }
 }
 
-// harmonic sums + threshold + compaction (kernels.cu:33-99 + :384-416 + peakfinder.hpp:77-86)
-__global__ void __launch_bounds__(256) harmonic_peaks_kernel(const float* __restrict__ P, int nbins, int nfolds,
-                                                             LevelRanges r, float thresh, int acc_idx,
-                                                             ps_raw_peak* __restrict__ peaks, unsigned* __restrict__ count,
-                                                             unsigned cap) {
-  const unsigned lane = threadIdx.x & 31;
-  for (int base = (blockIdx.x * blockDim.x + threadIdx.x) - (int)lane; base < nbins; base += gridDim.x * blockDim.x) {
-    int idx = base + (int)lane;
-    float v[6];
-    bool in = idx < nbins;
-    if (in) {
-      v[0] = __ldg(P + idx);
-      harmonic_folds(P, idx, nfolds, v + 1);
+struct PeakSink {
+  ps_raw_peak* peaks;
+  unsigned* count;
+  unsigned cap;
+};
+
+// harmonic sums + threshold + compaction (kernels.cu:33-99 + :384-416 + peakfinder.hpp:77-86).
+// A warp owns 512 consecutive bins; lane l holds bins base+32i (i < 16, base = chunk*512+l), so
+// for the fraction m/2^sh the read index is p0 + i*(32m >> sh): one index computation per
+// (thread, fraction), 16 loads at immediate offsets, and the 32 lanes of each load touch <= 2m+1
+// consecutive words (coalesced).  Sums are compared in the accumulator domain against a float
+// lower bound of thresh/scale: only bins that may exceed the threshold go through the reference's
+// double-precision scaling, so emitted values and decisions are bit-identical to it.
+struct LevelScales {
+  float lo[6];  // lower bound on the unscaled sum that can reach thresh at each level
+};
+
+template <bool FULL>
+__device__ __forceinline__ float hp_load(const float* __restrict__ q, int off, int idx, int nbins) {
+  if (FULL) return __ldg(q + off);
+  return idx < nbins ? __ldg(q + off) : 0.f;
+}
+
+#define PS_ADD_FRACTION(M_, SH_)                                                              \
+  {                                                                                           \
+    const float* __restrict__ q_ = P + ((base * (M_) + (1 << ((SH_)-1))) >> (SH_));           \
+    _Pragma("unroll") for (int i = 0; i < 16; i++)                                            \
+        acc[i] += hp_load<FULL>(q_, i * ((32 * (M_)) >> (SH_)), base + 32 * i, nbins);        \
+  }
+
+// Rare path: some of this warp's bins may exceed the threshold at level nh.  The flagged bins are
+// re-evaluated with the reference's per-bin arithmetic (harmonic_folds: same accumulation order,
+// double-precision scale factors), tested with the strict '>' and the level's bin range, and
+// appended to the peak list with one atomic per warp.
+__device__ __noinline__ void hp_emit_slow(const float* __restrict__ P, int nbins, int base, int lane, unsigned mask, int nh,
+                                          int nfolds, const LevelRanges& r, float thresh, int acc_idx, const PeakSink& sink) {
+#pragma unroll 1
+  for (int i = 0; i < 16; i++) {
+    if (!__any_sync(0xffffffffu, (mask >> i) & 1u)) continue;
+    const int idx = base + 32 * i;
+    bool hit = false;
+    float v = 0.f;
+    if (((mask >> i) & 1u) && idx < nbins) {
+      float f[5];
+      harmonic_folds(P, idx, nfolds, f);
+      v = nh == 0 ? __ldg(P + idx) : f[nh - 1];
+      hit = idx >= r.start[nh] && idx < r.limit[nh] && v > thresh;
     }
-#pragma unroll
-    for (int nh = 0; nh < 6; nh++) {
-      if (nh > nfolds) break;
-      bool hit = in && idx >= r.start[nh] && idx < r.limit[nh] && v[nh] > thresh;
-      unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (m) {
-        unsigned pos = 0;
-        if (lane == 0) pos = atomicAdd(count, (unsigned)__popc(m));
-        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1));
-        if (hit && pos < cap) {
-          ps_raw_peak pk;
-          pk.acc_idx = acc_idx;
-          pk.nh = nh;
-          pk.bin = idx;
-          pk.snr = v[nh];
-          peaks[pos] = pk;
-        }
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (m) {
+      unsigned pos = 0;
+      if (lane == 0) pos = atomicAdd(sink.count, (unsigned)__popc(m));
+      pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1));
+      if (hit && pos < sink.cap) {
+        ps_raw_peak pk;
+        pk.acc_idx = acc_idx;
+        pk.nh = nh;
+        pk.bin = idx;
+        pk.snr = v;
+        sink.peaks[pos] = pk;
       }
     }
   }
+}
+
+template <int NF, bool FULL>
+__device__ __forceinline__ void hp_chunk(const float* __restrict__ P, int nbins, int base, int lane, const LevelRanges& r,
+                                         const LevelScales& ls, float thresh, int acc_idx, const PeakSink& sink) {
+  float acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) acc[i] = hp_load<FULL>(P + base, 32 * i, base + 32 * i, nbins);
+
+  auto emit = [&](int nh) {
+    float mx = acc[0];
+#pragma unroll
+    for (int i = 1; i < 16; i++) mx = fmaxf(mx, acc[i]);
+    if (!__any_sync(0xffffffffu, mx > ls.lo[nh])) return;
+    unsigned mask = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) mask |= (acc[i] > ls.lo[nh]) ? (1u << i) : 0u;
+    hp_emit_slow(P, nbins, base, lane, mask, nh, NF, r, thresh, acc_idx, sink);
+  };
+
+  emit(0);
+  if (NF > 0) {
+    PS_ADD_FRACTION(1, 1)
+    emit(1);
+  }
+  if (NF > 1) {
+    PS_ADD_FRACTION(3, 2)
+    PS_ADD_FRACTION(1, 2)
+    emit(2);
+  }
+  if (NF > 2) {
+    PS_ADD_FRACTION(1, 3)
+    PS_ADD_FRACTION(3, 3)
+    PS_ADD_FRACTION(5, 3)
+    PS_ADD_FRACTION(7, 3)
+    emit(3);
+  }
+  if (NF > 3) {
+    PS_ADD_FRACTION(1, 4)
+    PS_ADD_FRACTION(3, 4)
+    PS_ADD_FRACTION(5, 4)
+    PS_ADD_FRACTION(7, 4)
+    PS_ADD_FRACTION(9, 4)
+    PS_ADD_FRACTION(11, 4)
+    PS_ADD_FRACTION(13, 4)
+    PS_ADD_FRACTION(15, 4)
+    emit(4);
+  }
+  if (NF > 4) {
+    PS_ADD_FRACTION(1, 5)
+    PS_ADD_FRACTION(3, 5)
+    PS_ADD_FRACTION(5, 5)
+    PS_ADD_FRACTION(7, 5)
+    PS_ADD_FRACTION(9, 5)
+    PS_ADD_FRACTION(11, 5)
+    PS_ADD_FRACTION(13, 5)
+    PS_ADD_FRACTION(15, 5)
+    PS_ADD_FRACTION(17, 5)
+    PS_ADD_FRACTION(19, 5)
+    PS_ADD_FRACTION(21, 5)
+    PS_ADD_FRACTION(23, 5)
+    PS_ADD_FRACTION(25, 5)
+    PS_ADD_FRACTION(27, 5)
+    PS_ADD_FRACTION(29, 5)
+    PS_ADD_FRACTION(31, 5)
+    emit(5);
+  }
+}
+
+// one warp = one chunk of 512 bins; blockIdx.y = batch item
+template <int NF>
+__global__ void __launch_bounds__(128) harmonic_peaks_kernel(const float* __restrict__ Pall, int nbins, size_t pstride,
+                                                             LevelRanges r, LevelScales ls, float thresh, int acc_idx0,
+                                                             PeakSink sink) {
+  const float* __restrict__ P = Pall + (size_t)blockIdx.y * pstride;
+  const int acc_idx = acc_idx0 + (int)blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (chunk * 512 >= nbins) return;
+  const int base = chunk * 512 + lane;
+  if (chunk * 512 + 512 <= nbins)
+    hp_chunk<NF, true>(P, nbins, base, lane, r, ls, thresh, acc_idx, sink);
+  else
+    hp_chunk<NF, false>(P, nbins, base, lane, r, ls, thresh, acc_idx, sink);
 }
 
 // mean of the first n u8 samples (GPU_mean on the converted floats, pipeline_multi.cu:161)
@@ -135,6 +276,10 @@ struct Search {
   unsigned* d_count = nullptr;
   unsigned cap = 0;
   LevelRanges ranges;
+  LevelScales scales;
+  float* d_pbatch = nullptr;   // kBatch spectra (stride pstride floats)
+  size_t pstride = 0;
+  const float* last_spectrum = nullptr;
   float bin_width_f = 0.f;   // float bin_width = 1.0/tobs   (pipeline_multi.cu:118-119)
   double bin_width = 0.0;    // stored as double in FrequencySeries (fourierseries.hpp:41)
 };
@@ -144,7 +289,7 @@ static void free_search(Search* s) {
   plan_destroy(s->plan);
   cudaFree(s->d_tim); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
-  cudaFree(s->d_peaks); cudaFree(s->d_count);
+  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch);
   delete s;
 }
 
@@ -180,7 +325,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   s->prm = *p;
   if (s->prm.boundary_5_freq <= 0) s->prm.boundary_5_freq = 0.05f;
   if (s->prm.boundary_25_freq <= 0) s->prm.boundary_25_freq = 0.5f;
-  int rc = plan_create(p->size, &s->plan);
+  int rc = plan_create(p->size, &s->plan, kAccelBatch);
   if (rc) {
     delete s;
     return rc;
@@ -193,6 +338,17 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   s->bin_width = bin_width;
   s->cap = p->max_peaks ? p->max_peaks : (1u << 20);
   level_ranges(s->prm, s->nbins, s->bin_width, &s->ranges);
+  {
+    // float32 lower bounds: a sum below thresh/scale*(1-4e-7) cannot exceed thresh after the
+    // reference's (float)((double)sum*scale); bounds are rounded toward -inf
+    const double sc[6] = {1.0, 1.0 / sqrt(2.0), 0.5, 1.0 / sqrt(8.0), 0.25, 1.0 / sqrt(32.0)};
+    for (int i = 0; i < 6; i++) {
+      double lo = (double)p->min_snr / sc[i];
+      lo -= fabs(lo) * 1e-6;
+      s->scales.lo[i] = nextafterf((float)lo, -INFINITY);
+    }
+    s->pstride = ((size_t)s->nbins + 63) & ~(size_t)63;
+  }
   size_t nb = s->nbins;
   cudaError_t e = cudaMalloc(&s->d_tim, sizeof(float) * size);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_X, sizeof(float2) * nb);
@@ -206,6 +362,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (e == cudaSuccess) e = cudaMemset(s->d_stats, 0, sizeof(float) * 4);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_peaks, sizeof(ps_raw_peak) * (size_t)s->cap);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_count, sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * kAccelBatch);
   if (e == cudaSuccess) e = cudaMemset(s->d_count, 0, sizeof(unsigned));
   if (e != cudaSuccess) {
     free_search(s);
@@ -249,7 +406,7 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   }
   LoadU8Padded ld{d_trial, s->d_stats + 3, valid, p->n2, 0};
   if ((rc = launch_pass1<false>(p, ld, st))) return rc;
-  StoreNatural sn{reinterpret_cast<float2*>(p->Z), p->n1, 0};
+  StoreNatural sn{reinterpret_cast<float2*>(p->Z), 0, 0, 0, nullptr};
   if ((rc = launch_pass2<false>(p, sn, st))) return rc;
   if ((rc = launch_r2c_post(p, p->Z, s->d_X, st))) return rc;
   if ((rc = ps_form_power_series((const ps_complex*)s->d_X, s->d_pspec, s->nbins, 0, st))) return rc;
@@ -264,7 +421,7 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   if ((rc = launch_stats(s->d_pspec, s->nbins, s->d_partials, s->d_stats, st))) return rc;
   LoadC2RPre lc{s->d_X, p->M, p->n2, 0};
   if ((rc = launch_pass1<true>(p, lc, st))) return rc;
-  StoreNatural so{reinterpret_cast<float2*>(s->d_tim), p->n1, 0};
+  StoreNatural so{reinterpret_cast<float2*>(s->d_tim), 0, 0, 0, nullptr};
   if ((rc = launch_pass2<true>(p, so, st))) return rc;
   if (h_mean || h_std) {
     float h[3];
@@ -283,19 +440,43 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   const ps_fft_plan_t* p = s->plan;
   unsigned size = s->prm.size;
   int rc;
-  for (int j = 0; j < n_acc; j++) {
-    LoadResampled ld{s->d_tim, accel_fact(h_acc[j], s->prm.tsamp), (double)size, p->n2, 0};
-    if ((rc = launch_pass1<false>(p, ld, st))) return rc;
-    StoreNatural sn{reinterpret_cast<float2*>(p->Z), p->n1, 0};
-    if ((rc = launch_pass2<false>(p, sn, st))) return rc;
-    spectrum_kernel<<<ew_grid(s->nbins, 256, 2), 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pspec, p->M,
-                                                               s->d_stats, (float)size);
+  PeakSink sink{s->d_peaks, s->d_count, s->cap};
+  for (int j = 0; j < n_acc; j += kAccelBatch) {
+    const int nb = std::min(kAccelBatch, n_acc - j);
+    LoadResampled ld;
+    ld.x = s->d_tim;
+    for (int b = 0; b < nb; b++) ld.afs.v[b] = accel_fact(h_acc[j + b], s->prm.tsamp);
+    ld.size = (double)size;
+    {
+      double amax = 0;
+      for (int b = 0; b < nb; b++) amax = std::max(amax, fabs(ld.afs.v[b]));
+      ld.max_shift = (float)(amax * 0.25 * (double)size * (double)size * 1.001);  // |i(i-N)| <= N^2/4
+      ld.max_step = (float)(amax * (double)size * 1.001);                         // |d/di| <= N
+    }
+    if ((rc = launch_pass1<false>(p, ld, st, nb))) return rc;
+    StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
+    if ((rc = launch_pass2<false>(p, sn, st, nb))) return rc;
+    dim3 g1(ew_grid(p->M / 4, 256, 1), nb);
+    spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
+                                        (float)size, p->TC, p->TD,
+                                        make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
     PS_LAUNCHED("spectrum_kernel");
-    harmonic_peaks_kernel<<<ew_grid(s->nbins, 256, 2), 256, 0, st>>>(s->d_pspec, (int)s->nbins, s->prm.nharmonics, s->ranges,
-                                                                     s->prm.min_snr, acc_idx0 + j, s->d_peaks, s->d_count,
-                                                                     s->cap);
+    dim3 g2((((unsigned)s->nbins + 511) / 512 + 3) / 4, nb);
+#define PS_HP(NF)                                                                                                       \
+  harmonic_peaks_kernel<NF><<<g2, 128, 0, st>>>(s->d_pbatch, (int)s->nbins, s->pstride, s->ranges, s->scales, s->prm.min_snr, \
+                                                 acc_idx0 + j, sink)
+    switch (s->prm.nharmonics) {
+      case 0: PS_HP(0); break;
+      case 1: PS_HP(1); break;
+      case 2: PS_HP(2); break;
+      case 3: PS_HP(3); break;
+      case 4: PS_HP(4); break;
+      default: PS_HP(5); break;
+    }
+#undef PS_HP
     PS_LAUNCHED("harmonic_peaks_kernel");
   }
+  s->last_spectrum = s->d_pbatch + (size_t)((n_acc - 1) % kAccelBatch) * s->pstride;
   return PS_OK;
 }
 
@@ -333,6 +514,6 @@ long ps_search_fetch_peaks(ps_search* hs, ps_raw_peak* h_out, size_t max_out, vo
 }
 
 const float* ps_search_whitened_series(ps_search* s) { return s ? SS(s)->d_tim : nullptr; }
-const float* ps_search_last_spectrum(ps_search* s) { return s ? SS(s)->d_pspec : nullptr; }
+const float* ps_search_last_spectrum(ps_search* s) { return s ? SS(s)->last_spectrum : nullptr; }
 
 }  // extern "C"

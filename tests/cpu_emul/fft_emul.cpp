@@ -26,7 +26,8 @@ std::vector<cf> roots(unsigned count, unsigned step, unsigned period) {
 
 struct Tables {
   std::vector<cf> W4096, TA, TB;
-  explicit Tables(unsigned M) : W4096(roots(4096, 1, 4096)), TA(roots(M / 4096 ? M / 4096 : 1, 4096, M)), TB(roots(4096, 1, M)) {}
+  unsigned M;
+  explicit Tables(unsigned M_) : M(M_), W4096(roots(4096, 1, 4096)), TA(roots(M_ / 4096 ? M_ / 4096 : 1, 4096, M_)), TB(roots(4096, 1, M_)) {}
   cf twiddle(unsigned p) const { return psfft::cmul(TA[p >> 12], TB[p & 4095u]); }
 };
 
@@ -40,10 +41,14 @@ struct StoreP1 {
   cf* Yt;
   const Tables* t;
   int n1, c0;
-  void operator()(int f, int k, cf v) const {
+  // same recurrence as StorePass1 in fft.cuh: W^(j2*(k0+stride*j)) = base * step^j
+  template <int R>
+  void store(int f, int k0, int stride, const cf* v) const {
     unsigned j2 = (unsigned)(c0 + f);
-    cf w = psfft::dirw<INV>(t->twiddle(j2 * (unsigned)k));
-    Yt[(size_t)j2 * n1 + k] = psfft::cmul(v, w);
+    cf base = psfft::dirw<INV>(t->twiddle(j2 * (unsigned)k0));
+    cf pw[R > 1 ? R : 2];
+    psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(t->twiddle((j2 * (unsigned)stride) % t->M)));
+    for (int j = 0; j < R; j++) Yt[(size_t)j2 * n1 + k0 + stride * j] = psfft::cmul(v[j], pw[j]);
   }
 };
 struct LoadP2 {
@@ -54,7 +59,10 @@ struct LoadP2 {
 struct StoreNat {
   cf* out;
   int n1, r0;
-  void operator()(int f, int k, cf v) const { out[(size_t)k * n1 + r0 + f] = v; }
+  template <int R>
+  void store(int f, int k0, int stride, const cf* v) const {
+    for (int j = 0; j < R; j++) out[(size_t)(k0 + stride * j) * n1 + r0 + f] = v[j];
+  }
 };
 
 template <int R3, bool INV, class L, class S>
