@@ -228,8 +228,10 @@ def main():
     prm = pb.PipelineParams(make_search_params(SIZE, NSAMPS, TSAMP, NFOLDS, 9.0), 1e-4, 16, 0.0, 0.0, 1.1, 64.0, 1382.0, -0.390625)
     offset = rank * ndm
 
+    pipe = pb.Pipeline(prm, zap=(ZAP_F, ZAP_W), device0=local, nworkers=1)
+
     def step(src):
-        recs, done = pb.pipeline_search(src, dms, prm, accs=ACCS, zap=(ZAP_F, ZAP_W), device0=local, nworkers=1, dm_idx_offset=offset)
+        recs, done = pipe.run(src, dms, accs=ACCS, dm_idx_offset=offset)
         merged = gather_candidates(recs, device=device) if world > 1 else recs
         return done, merged
 

@@ -206,6 +206,18 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
                         const float* h_zap_freqs, const float* h_zap_widths, int nzap, int device0,
                         int nworkers, ps_candidate* out, long max_out, unsigned long long* trials_done);
 
+/* The same with a long-lived handle: ps_pipeline_open builds every worker's device state once
+ * (search handles, FFT plans, streams, staging); ps_pipeline_run may then be called repeatedly
+ * (e.g. per batch of DM trials as dedispersion delivers them); results are those of
+ * ps_pipeline_search.  Not re-entrant per handle. */
+typedef struct ps_pipeline ps_pipeline;
+int ps_pipeline_open(const ps_pipeline_params* p, const float* h_zap_freqs, const float* h_zap_widths, int nzap,
+                     int device0, int nworkers, ps_pipeline** out);
+long ps_pipeline_run(ps_pipeline* h, const unsigned char* h_trials, const float* h_dm_list, int ndm,
+                     int dm_idx_offset, const float* h_acc_explicit, int n_acc_explicit, ps_candidate* out,
+                     long max_out, unsigned long long* trials_done);
+void ps_pipeline_close(ps_pipeline* h);
+
 /* Diagnostics of the last ps_pipeline_search call of this process, summed over workers:
  * seconds spent queueing device work, waiting for the device, and in host-side clustering +
  * distillation, then the number of raw above-threshold bins fetched. */

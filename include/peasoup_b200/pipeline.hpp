@@ -48,6 +48,62 @@ class DMDispenser {  // pipeline_multi.cu:33-81 (progress bar omitted)
   }
 };
 
+// Device-side state of one worker: two DM trials in flight (search handle, stream, staging).
+// Creating it costs ~40 cudaMalloc calls and table uploads, so a long-lived pipeline keeps it
+// across calls (ps_pipeline_open); a one-shot Worker builds its own.
+class WorkerSlots {
+ public:
+  struct Slot {
+    ps_search* search = 0;
+    cudaStream_t stream = 0;
+    unsigned char* d_trial = 0;
+    std::vector<ps_raw_peak> peaks;
+    std::vector<float> acc_list;
+    int ii = -1;
+    float dm = 0.f;
+  };
+  Slot slots[2];
+  int device;
+  ps_search_params prm;
+  size_t ncopy;
+
+  WorkerSlots(int device, const ps_search_params& prm, const std::vector<float>& zf, const std::vector<float>& zw)
+      : device(device), prm(prm), ncopy(std::min(prm.nsamps, prm.size)) {
+    ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
+    const unsigned cap = prm.max_peaks ? prm.max_peaks : (1u << 20);
+    try {
+      for (int i = 0; i < 2; i++) {
+        ErrorChecker::check(ps_search_create(&this->prm, &slots[i].search));
+        if (!zf.empty()) ErrorChecker::check(ps_search_set_zaplist(slots[i].search, &zf[0], &zw[0], (unsigned)zf.size()));
+        ErrorChecker::check_cuda_error(cudaStreamCreateWithFlags(&slots[i].stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        Utils::device_malloc(&slots[i].d_trial, ncopy);
+        slots[i].peaks.resize(cap);
+      }
+    } catch (...) {
+      release();
+      throw;
+    }
+  }
+  ~WorkerSlots() { release(); }
+  WorkerSlots(const WorkerSlots&) = delete;
+  bool matches(const ps_search_params& o) const {
+    return o.size == prm.size && o.nsamps == prm.nsamps && o.tsamp == prm.tsamp && o.nharmonics == prm.nharmonics &&
+           o.min_snr == prm.min_snr && o.min_freq == prm.min_freq && o.max_freq == prm.max_freq && o.max_peaks == prm.max_peaks;
+  }
+
+ private:
+  void release() {
+    cudaSetDevice(device);
+    for (int i = 0; i < 2; i++) {
+      if (slots[i].stream) cudaStreamSynchronize(slots[i].stream);
+      ps_search_destroy(slots[i].search);
+      cudaFree(slots[i].d_trial);
+      if (slots[i].stream) cudaStreamDestroy(slots[i].stream);
+      slots[i] = Slot();
+    }
+  }
+};
+
 class Worker {  // pipeline_multi.cu:83-254
   DispersionTrials<unsigned char>& trials;
   DMDispenser& manager;
@@ -58,15 +114,8 @@ class Worker {  // pipeline_multi.cu:83-254
   const std::vector<float>* fixed_accs;  // when set, replaces acc_plan (benchmarks / parity harness)
   int dm_idx_offset;
 
-  struct Slot {
-    ps_search* search = 0;
-    cudaStream_t stream = 0;
-    unsigned char* d_trial = 0;
-    std::vector<ps_raw_peak> peaks;
-    std::vector<float> acc_list;
-    int ii = -1;
-    float dm = 0.f;
-  };
+  typedef WorkerSlots::Slot Slot;
+  WorkerSlots* shared_slots;
 
  public:
   CandidateCollection dm_trial_cands;
@@ -77,16 +126,16 @@ class Worker {  // pipeline_multi.cu:83-254
   unsigned long long raw_peaks = 0;
 
   Worker(DispersionTrials<unsigned char>& trials, DMDispenser& manager, AccelerationPlan& acc_plan, SearchArgs& args,
-         unsigned int size, int device, const std::vector<float>* fixed_accs = 0, int dm_idx_offset = 0)
+         unsigned int size, int device, const std::vector<float>* fixed_accs = 0, int dm_idx_offset = 0,
+         WorkerSlots* shared_slots = 0)
       : trials(trials), manager(manager), args(args), acc_plan(acc_plan), size(size), device(device), fixed_accs(fixed_accs),
-        dm_idx_offset(dm_idx_offset) {}
+        dm_idx_offset(dm_idx_offset), shared_slots(shared_slots) {}
 
-  void start() {
-    ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
+  static ps_search_params search_params(SearchArgs& args, unsigned int size, unsigned int nsamps, float tsamp) {
     ps_search_params prm;
     prm.size = size;
-    prm.nsamps = trials.get_nsamps();
-    prm.tsamp = trials.get_tsamp();
+    prm.nsamps = nsamps;
+    prm.tsamp = tsamp;
     prm.nharmonics = args.nharmonics;
     prm.min_snr = args.min_snr;
     prm.min_freq = args.min_freq;
@@ -94,7 +143,12 @@ class Worker {  // pipeline_multi.cu:83-254
     prm.boundary_5_freq = 0.05f;
     prm.boundary_25_freq = 0.5f;
     prm.max_peaks = args.max_peaks;
-    const unsigned cap = prm.max_peaks ? prm.max_peaks : (1u << 20);
+    return prm;
+  }
+
+  void start() {
+    ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
+    ps_search_params prm = search_params(args, size, trials.get_nsamps(), trials.get_tsamp());
 
     std::vector<float> zf = args.zap_freqs, zw = args.zap_widths;
     if (args.zapfilename != "") Zapper::parse(args.zapfilename, zf, zw);
@@ -109,25 +163,14 @@ class Worker {  // pipeline_multi.cu:83-254
     AccelerationDistiller acc_still(tobs, args.freq_tol, true);          // :139
     const size_t ncopy = std::min(trials.get_nsamps(), size);
 
-    Slot slots[2];
-    struct Cleanup {
-      Slot* s;
-      ~Cleanup() {
-        for (int i = 0; i < 2; i++) {
-          if (s[i].stream) cudaStreamSynchronize(s[i].stream);
-          ps_search_destroy(s[i].search);
-          cudaFree(s[i].d_trial);
-          if (s[i].stream) cudaStreamDestroy(s[i].stream);
-        }
-      }
-    } cleanup{slots};
-    for (int i = 0; i < 2; i++) {
-      ErrorChecker::check(ps_search_create(&prm, &slots[i].search));
-      if (!zf.empty()) ErrorChecker::check(ps_search_set_zaplist(slots[i].search, &zf[0], &zw[0], (unsigned)zf.size()));
-      ErrorChecker::check_cuda_error(cudaStreamCreateWithFlags(&slots[i].stream, cudaStreamNonBlocking), "cudaStreamCreate");
-      Utils::device_malloc(&slots[i].d_trial, ncopy);
-      slots[i].peaks.resize(cap);
-    }
+    WorkerSlots* own = 0;
+    struct Owner {
+      WorkerSlots*& p;
+      ~Owner() { delete p; }
+    } owner{own};
+    WorkerSlots* ws = shared_slots;
+    if (!ws || !ws->matches(prm) || ws->device != device) ws = own = new WorkerSlots(device, prm, zf, zw);
+    Slot* slots = ws->slots;
 
     std::vector<int> idxs, peakidxs;
     std::vector<float> snrs, peaksnrs, peakfreqs;

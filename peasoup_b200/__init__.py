@@ -51,7 +51,8 @@ SYMBOLS = [
     "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
     "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks",
     "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
-    "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile",
+    "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
+    "ps_pipeline_run", "ps_pipeline_close",
     "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
 ]
 
@@ -98,6 +99,9 @@ def load() -> C.CDLL:
         "ps_search_whitened_series": [vp], "ps_search_last_spectrum": [vp],
         "ps_pipeline_search": [C.POINTER(PipelineParams), vp, vp, i, i, vp, i, vp, vp, i, i, i, vp, C.c_long,
                                C.POINTER(C.c_ulonglong)],
+        "ps_pipeline_open": [C.POINTER(PipelineParams), vp, vp, i, i, i, C.POINTER(vp)],
+        "ps_pipeline_run": [vp, vp, vp, i, i, vp, i, vp, C.c_long, C.POINTER(C.c_ulonglong)],
+        "ps_pipeline_close": [vp],
         "ps_accel_plan_generate": [f, f, f, f, u, f, f, f, f, vp, i],
         "ps_cluster_peaks": [vp, vp, i, i, vp, vp],
         "ps_peak_range": [i, d, i, f, f, C.POINTER(i), C.POINTER(i), C.POINTER(f)],
@@ -113,6 +117,8 @@ def load() -> C.CDLL:
     lib.ps_pipeline_profile.restype = None
     lib.ps_search_fetch_peaks.restype = C.c_long
     lib.ps_pipeline_search.restype = C.c_long
+    lib.ps_pipeline_run.restype = C.c_long
+    lib.ps_pipeline_close.restype = None
     lib.ps_distill.restype = C.c_long
     lib.ps_search_whitened_series.restype = vp
     lib.ps_search_last_spectrum.restype = vp
@@ -137,5 +143,5 @@ def ptr(t) -> int:
     return t.ctypes.data
 
 
-from .host import (FFTPlan, Search, accel_plan, cluster_peaks, distill, peak_range,  # noqa: E402
+from .host import (FFTPlan, Pipeline, Search, accel_plan, cluster_peaks, distill, peak_range,  # noqa: E402
                    pipeline_search)

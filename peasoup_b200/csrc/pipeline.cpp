@@ -33,16 +33,28 @@ static long flatten(std::vector<Candidate>& cands, ps_candidate* out, long max_o
 
 extern "C" {
 
-long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_trials, const float* h_dm_list, int ndm,
-                        int dm_idx_offset, const float* h_acc_explicit, int n_acc_explicit, const float* h_zap_freqs,
-                        const float* h_zap_widths, int nzap, int device0, int nworkers, ps_candidate* out, long max_out,
-                        unsigned long long* trials_done) {
+struct ps_pipeline {
+  ps_pipeline_params prm;
+  SearchArgs args;
+  unsigned size;
+  int device0, nworkers;
+  std::vector<WorkerSlots*> slots;
+  ~ps_pipeline() {
+    for (size_t i = 0; i < slots.size(); i++) delete slots[i];
+  }
+};
+
+int ps_pipeline_open(const ps_pipeline_params* p, const float* h_zap_freqs, const float* h_zap_widths, int nzap, int device0,
+                     int nworkers, ps_pipeline** out) {
+  ps_pipeline* h = 0;
   try {
-    if (!p || (!h_trials && ndm > 0)) ErrorChecker::throw_error("ps_pipeline_search: null argument");
+    if (!p || !out) ErrorChecker::throw_error("ps_pipeline_open: null argument");
     if (nworkers < 1) nworkers = 1;
-    std::vector<float> dms(h_dm_list, h_dm_list + ndm);
-    DispersionTrials<unsigned char> trials(const_cast<unsigned char*>(h_trials), p->search.nsamps, p->search.tsamp, dms);
-    SearchArgs args;
+    h = new ps_pipeline();
+    h->prm = *p;
+    h->device0 = device0;
+    h->nworkers = nworkers;
+    SearchArgs& args = h->args;
     args.size = p->search.size;
     args.nharmonics = p->search.nharmonics;
     args.min_snr = p->search.min_snr;
@@ -55,8 +67,30 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
       args.zap_freqs.assign(h_zap_freqs, h_zap_freqs + nzap);
       args.zap_widths.assign(h_zap_widths, h_zap_widths + nzap);
     }
-    unsigned size = args.size ? args.size : Utils::prev_power_of_two(p->search.nsamps);
-    AccelerationPlan acc_plan(p->acc_start, p->acc_end, p->acc_tol, p->acc_pulse_width, size, p->search.tsamp, p->cfreq, p->foff);
+    h->size = args.size ? args.size : Utils::prev_power_of_two(p->search.nsamps);
+    ps_search_params sp = Worker::search_params(args, h->size, p->search.nsamps, p->search.tsamp);
+    for (int i = 0; i < nworkers; i++) h->slots.push_back(new WorkerSlots(device0 + i, sp, args.zap_freqs, args.zap_widths));
+    *out = h;
+    return PS_OK;
+  } catch (std::exception& e) {
+    delete h;
+    ps::set_error(e.what());
+    return PS_ECUDA;
+  }
+}
+
+void ps_pipeline_close(ps_pipeline* h) { delete h; }
+
+long ps_pipeline_run(ps_pipeline* h, const unsigned char* h_trials, const float* h_dm_list, int ndm, int dm_idx_offset,
+                     const float* h_acc_explicit, int n_acc_explicit, ps_candidate* out, long max_out,
+                     unsigned long long* trials_done) {
+  try {
+    if (!h || (!h_trials && ndm > 0)) ErrorChecker::throw_error("ps_pipeline_run: null argument");
+    const ps_pipeline_params* p = &h->prm;
+    const int nworkers = h->nworkers;
+    std::vector<float> dms(h_dm_list, h_dm_list + ndm);
+    DispersionTrials<unsigned char> trials(const_cast<unsigned char*>(h_trials), p->search.nsamps, p->search.tsamp, dms);
+    AccelerationPlan acc_plan(p->acc_start, p->acc_end, p->acc_tol, p->acc_pulse_width, h->size, p->search.tsamp, p->cfreq, p->foff);
     std::vector<float> fixed;
     if (n_acc_explicit > 0) fixed.assign(h_acc_explicit, h_acc_explicit + n_acc_explicit);
     DMDispenser dispenser(trials);
@@ -64,24 +98,31 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
     std::vector<std::thread> threads;
     std::vector<std::exception_ptr> errors(nworkers);
     for (int i = 0; i < nworkers; i++)
-      workers.push_back(new Worker(trials, dispenser, acc_plan, args, size, device0 + i, n_acc_explicit > 0 ? &fixed : 0, dm_idx_offset));
-    for (int i = 0; i < nworkers; i++)
-      threads.emplace_back([&, i]() {
-        try {
-          workers[i]->start();
-        } catch (...) {
-          errors[i] = std::current_exception();
-        }
-      });
-    for (auto& t : threads) t.join();
+      workers.push_back(new Worker(trials, dispenser, acc_plan, h->args, h->size, h->device0 + i, n_acc_explicit > 0 ? &fixed : 0,
+                                   dm_idx_offset, h->slots[i]));
+    if (nworkers == 1) {
+      try {
+        workers[0]->start();
+      } catch (...) {
+        errors[0] = std::current_exception();
+      }
+    } else {
+      for (int i = 0; i < nworkers; i++)
+        threads.emplace_back([&, i]() {
+          try {
+            workers[i]->start();
+          } catch (...) {
+            errors[i] = std::current_exception();
+          }
+        });
+      for (auto& t : threads) t.join();
+    }
     CandidateCollection dm_cands;
     unsigned long long done = 0;
+    g_prof[0] = g_prof[1] = g_prof[2] = g_prof[3] = 0;
     for (int i = 0; i < nworkers; i++) {
       dm_cands.append(workers[i]->dm_trial_cands.cands);
       done += workers[i]->trials_done;
-    }
-    g_prof[0] = g_prof[1] = g_prof[2] = g_prof[3] = 0;
-    for (int i = 0; i < nworkers; i++) {
       g_prof[0] += workers[i]->t_submit;
       g_prof[1] += workers[i]->t_wait;
       g_prof[2] += workers[i]->t_host;
@@ -99,6 +140,22 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
     ps::set_error(e.what());
     return PS_ECUDA;
   }
+}
+
+long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_trials, const float* h_dm_list, int ndm,
+                        int dm_idx_offset, const float* h_acc_explicit, int n_acc_explicit, const float* h_zap_freqs,
+                        const float* h_zap_widths, int nzap, int device0, int nworkers, ps_candidate* out, long max_out,
+                        unsigned long long* trials_done) {
+  if (ndm <= 0) {
+    if (trials_done) *trials_done = 0;
+    return 0;
+  }
+  ps_pipeline* h = 0;
+  int rc = ps_pipeline_open(p, h_zap_freqs, h_zap_widths, nzap, device0, nworkers, &h);
+  if (rc) return rc;
+  long n = ps_pipeline_run(h, h_trials, h_dm_list, ndm, dm_idx_offset, h_acc_explicit, n_acc_explicit, out, max_out, trials_done);
+  ps_pipeline_close(h);
+  return n;
 }
 
 void ps_pipeline_profile(double* out4) {

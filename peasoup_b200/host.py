@@ -157,3 +157,35 @@ def pipeline_search(trials_u8, dm_list, params: PipelineParams, accs=None, zap=N
     if n > max_out:
         raise RuntimeError(f"candidate buffer too small: {n} > {max_out}")
     return out[:n].copy(), done.value
+
+
+class Pipeline:
+    """ps_pipeline handle: worker device state built once, run() per batch of DM trials."""
+
+    def __init__(self, params: PipelineParams, zap=None, device0=0, nworkers=1, max_out=1 << 20):
+        zf = np.ascontiguousarray(zap[0] if zap else [], np.float32)
+        zw = np.ascontiguousarray(zap[1] if zap else [], np.float32)
+        self._h = C.c_void_p()
+        self._out = np.zeros(max_out, CAND_DTYPE)
+        check(load().ps_pipeline_open(C.byref(params), ptr(zf), ptr(zw), len(zf), device0, nworkers, C.byref(self._h)))
+
+    def run(self, trials_u8, dm_list, accs=None, dm_idx_offset=0):
+        dm = np.ascontiguousarray(dm_list, np.float32)
+        a = np.ascontiguousarray(accs if accs is not None else [], np.float32)
+        done = C.c_ulonglong(0)
+        n = check(load().ps_pipeline_run(self._h, ptr(trials_u8), ptr(dm), len(dm), dm_idx_offset, ptr(a), len(a),
+                                         ptr(self._out), len(self._out), C.byref(done)))
+        if n > len(self._out):
+            raise RuntimeError(f"candidate buffer too small: {n} > {len(self._out)}")
+        return self._out[:n].copy(), done.value
+
+    def close(self):
+        if self._h:
+            load().ps_pipeline_close(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
