@@ -11,6 +11,7 @@
 // trial i+1.  Candidate output is identical in content and order to the staged path.
 #pragma once
 #include <chrono>
+#include <cstdlib>
 #include <mutex>
 #include <thread>
 #include "transforms.hpp"
@@ -62,17 +63,23 @@ class WorkerSlots {
     int ii = -1;
     float dm = 0.f;
   };
-  Slot slots[2];
+  enum { kMaxSlots = 4 };
+  Slot slots[kMaxSlots];
+  int nslots;
   int device;
   ps_search_params prm;
   size_t ncopy;
 
   WorkerSlots(int device, const ps_search_params& prm, const std::vector<float>& zf, const std::vector<float>& zw)
       : device(device), prm(prm), ncopy(std::min(prm.nsamps, prm.size)) {
+    // DM trials in flight per worker: their kernels interleave on the device (different streams)
+    // and hide each other's latency; PS_SLOTS overrides the default of 4
+    nslots = 4;
+    if (const char* e = getenv("PS_SLOTS")) nslots = std::max(1, std::min((int)kMaxSlots, atoi(e)));
     ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
     const unsigned cap = prm.max_peaks ? prm.max_peaks : (1u << 20);
     try {
-      for (int i = 0; i < 2; i++) {
+      for (int i = 0; i < nslots; i++) {
         ErrorChecker::check(ps_search_create(&this->prm, &slots[i].search));
         if (!zf.empty()) ErrorChecker::check(ps_search_set_zaplist(slots[i].search, &zf[0], &zw[0], (unsigned)zf.size()));
         ErrorChecker::check_cuda_error(cudaStreamCreateWithFlags(&slots[i].stream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -94,7 +101,7 @@ class WorkerSlots {
  private:
   void release() {
     cudaSetDevice(device);
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < kMaxSlots; i++) {
       if (slots[i].stream) cudaStreamSynchronize(slots[i].stream);
       ps_search_destroy(slots[i].search);
       cudaFree(slots[i].d_trial);
@@ -234,13 +241,28 @@ class Worker {  // pipeline_multi.cu:83-254
       t_host += secs(t1, clk::now());
     };
 
-    int cur = 0;
-    bool live = submit(slots[cur]);
-    while (live) {
-      bool next_live = submit(slots[cur ^ 1]);
-      finish(slots[cur]);
-      cur ^= 1;
-      live = next_live;
+    // ring of DM trials in flight: keep every slot busy, retire in submission order
+    const int K = ws->nslots;
+    int head = 0, tail = 0, inflight = 0;
+    bool more = true;
+    while (more && inflight < K) {
+      more = submit(slots[head]);
+      if (more) {
+        head = (head + 1) % K;
+        inflight++;
+      }
+    }
+    while (inflight) {
+      finish(slots[tail]);
+      tail = (tail + 1) % K;
+      inflight--;
+      if (more) {
+        more = submit(slots[head]);
+        if (more) {
+          head = (head + 1) % K;
+          inflight++;
+        }
+      }
     }
   }
 };

@@ -189,6 +189,7 @@ struct StorePass1 {
   cf* Yt;
   FftTables t;
   int n1, c0;
+  int n2, tw;  // Yt is tiled for pass 2: Yt[k1 / tw][j2][k1 % tw], tw = rows per pass-2 tile
   // outputs k = k0 + stride*j of column j2: multiply by W_M^(j2*k) = base * step^j (two
   // interleaved chains, <= R/2 roundings deep) and store the column run
   template <int R>
@@ -197,24 +198,24 @@ struct StorePass1 {
     const cf base = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k0));
     cf pw[R > 1 ? R : 2];
     psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride)));
-    float2* col = reinterpret_cast<float2*>(Yt) + (size_t)j2 * n1 + k0;
+    float2* out = reinterpret_cast<float2*>(Yt) + (size_t)j2 * tw;
+    const unsigned twm = (unsigned)tw - 1u;  // tw is a power of two
 #pragma unroll
     for (int j = 0; j < R; j++) {
       cf o = psfft::cmul(v[j], pw[j]);
-      col[stride * j] = make_float2(o.x, o.y);
+      const unsigned k = (unsigned)(k0 + stride * j);
+      out[(size_t)(k & ~twm) * n2 + (k & twm)] = make_float2(o.x, o.y);
     }
   }
 };
 
 struct LoadPass2 {
-  static constexpr bool kAsync = true;
-  __device__ __forceinline__ void prefetch(int f, int idx, cf* dst) const {
-    cp_async8(dst, &Yt[(size_t)idx * n1 + r0 + f]);
-  }
   const cf* Yt;
   int n1, r0;
+  int n2, tw;
+  // tile r0/tw of Yt[k1 / tw][j2][k1 % tw]: the whole tile is one contiguous run
   __device__ __forceinline__ cf operator()(int f, int idx) const {
-    float2 v = reinterpret_cast<const float2*>(Yt)[(size_t)idx * n1 + r0 + f];
+    float2 v = reinterpret_cast<const float2*>(Yt)[((size_t)(r0 / tw) * n2 + idx) * tw + f];
     return psfft::mk(v.x, v.y);
   }
 };
@@ -250,7 +251,7 @@ __device__ __forceinline__ void load_operands(const Loader& ld, cf* v) {
 
 // grid-stride over (batch item, tile); items are independent transforms with their own Yt slice
 template <int R3, bool INV, class Loader>
-__global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, FftTables t, int n1, int n2, int nbatch) {
+__global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, FftTables t, int n1, int n2, int nbatch, int tw2) {
   using C = psfft::CtaFft<R3, INV>;
   extern __shared__ float smem[];
   const int ntiles = n2 / C::F;
@@ -263,7 +264,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, Ff
   load_operands<C>(ld, v);
   for (; work < nwork; work += gridDim.x) {
     const int b = work / ntiles, tile = work - b * ntiles;
-    StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F};
+    StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F, n2, tw2};
     C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
     __syncthreads();
     C::phaseB(threadIdx.x, smem, t.W4096, st);
@@ -288,7 +289,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
   if (work >= nwork) return;
   cf v[16];
   {
-    LoadPass2 ld{Yt + (size_t)(work / ntiles) * M, n1, (work % ntiles) * C::F};
+    LoadPass2 ld{Yt + (size_t)(work / ntiles) * M, n1, (work % ntiles) * C::F, n2, C::F};
     load_operands<C>(ld, v);
   }
   for (; work < nwork; work += gridDim.x) {
@@ -300,7 +301,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
     __syncthreads();
     const int next = work + gridDim.x;
     if (next < nwork) {
-      LoadPass2 ld{Yt + (size_t)(next / ntiles) * M, n1, (next % ntiles) * C::F};
+      LoadPass2 ld{Yt + (size_t)(next / ntiles) * M, n1, (next % ntiles) * C::F, n2, C::F};
       load_operands<C>(ld, v);
     }
     C::phaseC(threadIdx.x, smem, st);
@@ -330,7 +331,7 @@ inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t
   const size_t smem = C::SMEM_BYTES;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
-  k<<<fft_grid(p->n2 / C::F * nbatch), C::THREADS, smem, st>>>(ld, p->Yt, p->tables(), p->n1, p->n2, nbatch);
+  k<<<fft_grid(p->n2 / C::F * nbatch), C::THREADS, smem, st>>>(ld, p->Yt, p->tables(), p->n1, p->n2, nbatch, 32 / p->r2);
   PS_LAUNCHED("fft_pass1_kernel");
   return PS_OK;
 }

@@ -41,6 +41,7 @@ struct StoreP1 {
   cf* Yt;
   const Tables* t;
   int n1, c0;
+  int n2, tw;
   // same recurrence as StorePass1 in fft.cuh: W^(j2*(k0+stride*j)) = base * step^j
   template <int R>
   void store(int f, int k0, int stride, const cf* v) const {
@@ -48,13 +49,17 @@ struct StoreP1 {
     cf base = psfft::dirw<INV>(t->twiddle(j2 * (unsigned)k0));
     cf pw[R > 1 ? R : 2];
     psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(t->twiddle((j2 * (unsigned)stride) % t->M)));
-    for (int j = 0; j < R; j++) Yt[(size_t)j2 * n1 + k0 + stride * j] = psfft::cmul(v[j], pw[j]);
+    for (int j = 0; j < R; j++) {
+      int k = k0 + stride * j;
+      Yt[((size_t)(k / tw) * n2 + j2) * tw + k % tw] = psfft::cmul(v[j], pw[j]);
+    }
   }
 };
 struct LoadP2 {
   const cf* Yt;
   int n1, r0;
-  cf operator()(int f, int idx) const { return Yt[(size_t)idx * n1 + r0 + f]; }
+  int n2, tw;
+  cf operator()(int f, int idx) const { return Yt[((size_t)(r0 / tw) * n2 + idx) * tw + f]; }
 };
 struct StoreNat {
   cf* out;
@@ -75,12 +80,12 @@ void run_tile(std::vector<float>& smem, const Tables& t, const L& ld, const S& s
 }
 
 template <int R3, bool INV>
-void pass1(const cf* in, cf* Yt, const Tables& t, int n1, int n2) {
+void pass1(const cf* in, cf* Yt, const Tables& t, int n1, int n2, int tw2) {
   using C = psfft::CtaFft<R3, INV>;
   std::vector<float> smem;
   for (int tile = 0; tile < n2 / C::F; tile++) {
     LoadCols ld{in, n2, tile * C::F};
-    StoreP1<INV> st{Yt, &t, n1, tile * C::F};
+    StoreP1<INV> st{Yt, &t, n1, tile * C::F, n2, tw2};
     run_tile<R3, INV>(smem, t, ld, st);
   }
 }
@@ -89,7 +94,7 @@ void pass2(const cf* Yt, cf* out, const Tables& t, int n1, int n2) {
   using C = psfft::CtaFft<R3, INV>;
   std::vector<float> smem;
   for (int tile = 0; tile < n1 / C::F; tile++) {
-    LoadP2 ld{Yt, n1, tile * C::F};
+    LoadP2 ld{Yt, n1, tile * C::F, n2, C::F};
     StoreNat st{out, n1, tile * C::F};
     run_tile<R3, INV>(smem, t, ld, st);
   }
@@ -110,7 +115,7 @@ int cfft(int n1, int n2, const cf* in, cf* out) {
   unsigned M = (unsigned)n1 * n2;
   Tables t(M);
   std::vector<cf> Yt(M);
-  DISPATCH(n1 / 256, pass1, in, Yt.data(), t, n1, n2)
+  DISPATCH(n1 / 256, pass1, in, Yt.data(), t, n1, n2, 32 / (n2 / 256))
   DISPATCH(n2 / 256, pass2, Yt.data(), out, t, n1, n2)
   return 0;
 }
