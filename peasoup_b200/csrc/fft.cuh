@@ -93,12 +93,15 @@ struct AccelFacts {
 // shift i*af*(i-N) decides it whenever it lies safely away from a rounding boundary (the shift is
 // then rn(shift32)); otherwise the reference's FP64 expression is evaluated.
 struct LoadResampled {
-  static constexpr bool kAsync = true;
-  const float* x;
+  // The whitened series is kept TRANSPOSED as complex pairs: pair e = (x[2e], x[2e+1]) of the natural
+  // series lives at D[(e % n2) * n1 + e / n2], so the column a pass-1 tile transforms is a contiguous
+  // run in memory.  A warp's load then touches 4 runs of 64 bytes instead of 8 scattered sectors.
+  const float2* D;
   AccelFacts afs;
   double size;
   float max_shift;  // host bound on |i*af*(i-N)| over the series, all batch items
   float max_step;   // host bound on |shift(i+1) - shift(i)|
+  int n1, lg_n2;
   double af;
   float af32, fsize, thr;
   int n2, c0;
@@ -126,16 +129,37 @@ struct LoadResampled {
       *i1 = (unsigned)resample_index_II(af, size, i + 1);
     }
   }
+  __device__ __forceinline__ size_t pair_addr(unsigned e) const {
+    return (size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2);
+  }
   __device__ __forceinline__ cf operator()(int f, int idx) const {
     unsigned i0, i1;
     indices(f, idx, &i0, &i1);
-    return psfft::mk(__ldg(&x[i0]), __ldg(&x[i1]));
+    if (((i0 & 1u) == 0) && i1 == i0 + 1) {  // both samples in one pair: one 8-byte load
+      float2 v = __ldg(&D[pair_addr(i0 >> 1)]);
+      return psfft::mk(v.x, v.y);
+    }
+    const float* Df = reinterpret_cast<const float*>(D);
+    return psfft::mk(__ldg(&Df[2 * pair_addr(i0 >> 1) + (i0 & 1u)]), __ldg(&Df[2 * pair_addr(i1 >> 1) + (i1 & 1u)]));
   }
-  __device__ __forceinline__ void prefetch(int f, int idx, cf* dst) const {
-    unsigned i0, i1;
-    indices(f, idx, &i0, &i1);
-    cp_async4(&dst->x, &x[i0]);
-    cp_async4(&dst->y, &x[i1]);
+};
+
+// C2R output storer writing the transposed pair layout LoadResampled reads: time pair e = k1 + n1*k2
+struct StoreTransposedPairs {
+  float2* D;
+  int n1, r0;
+  int lg_n2;
+  __device__ __forceinline__ void begin(int, int first, int n) {
+    r0 = first;
+    n1 = n;
+  }
+  template <int R>
+  __device__ __forceinline__ void store(int f, int k0, int stride, const cf* v) const {
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+      const unsigned e = (unsigned)(r0 + f) + (unsigned)n1 * (unsigned)(k0 + stride * j);
+      D[(size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2)] = make_float2(v[j].x, v[j].y);
+    }
   }
 };
 

@@ -245,6 +245,12 @@ __global__ void __launch_bounds__(128) harmonic_peaks_kernel(const float* __rest
     hp_chunk<NF, false>(P, nbins, base, lane, r, ls, thresh, acc_idx, sink);
 }
 
+__global__ void __launch_bounds__(256) untranspose_pairs_kernel(const float2* __restrict__ D, float2* __restrict__ out, unsigned M,
+                                                                int n1, int lg_n2) {
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < M; e += gridDim.x * blockDim.x)
+    out[e] = D[(size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2)];
+}
+
 // mean of the first n u8 samples (GPU_mean on the converted floats, pipeline_multi.cu:161)
 __global__ void __launch_bounds__(256) u8_sum_kernel(const unsigned char* __restrict__ b, size_t n, unsigned long long* __restrict__ acc) {
   unsigned long long s = 0;
@@ -261,7 +267,9 @@ struct Search {
   ps_search_params prm;
   ps_fft_plan_t* plan = nullptr;
   unsigned nbins = 0;
-  float* d_tim = nullptr;      // size floats: whitened series
+  float* d_tim = nullptr;      // whitened series as size/2 complex pairs, TRANSPOSED (see LoadResampled)
+  float* d_tim_nat = nullptr;  // natural-order copy, made on request (ps_search_whitened_series)
+  int lg_n2 = 0;
   float2* d_X = nullptr;       // nbins complex
   float* d_pspec = nullptr;    // nbins
   float* d_median = nullptr;   // nbins
@@ -287,7 +295,7 @@ struct Search {
 static void free_search(Search* s) {
   if (!s) return;
   plan_destroy(s->plan);
-  cudaFree(s->d_tim); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
+  cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
   cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch);
   delete s;
@@ -332,6 +340,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   }
   unsigned size = p->size;
   s->nbins = size / 2 + 1;
+  while ((1 << s->lg_n2) < s->plan->n2) s->lg_n2++;
   float tobs = size * p->tsamp;            // pipeline_multi.cu:118
   float bin_width = 1.0 / tobs;            // :119
   s->bin_width_f = bin_width;
@@ -421,7 +430,7 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   if ((rc = launch_stats(s->d_pspec, s->nbins, s->d_partials, s->d_stats, st))) return rc;
   LoadC2RPre lc{s->d_X, p->M, p->n2, 0};
   if ((rc = launch_pass1<true>(p, lc, st))) return rc;
-  StoreNatural so{reinterpret_cast<float2*>(s->d_tim), 0, 0, 0, nullptr};
+  StoreTransposedPairs so{reinterpret_cast<float2*>(s->d_tim), 0, 0, s->lg_n2};
   if ((rc = launch_pass2<true>(p, so, st))) return rc;
   if (h_mean || h_std) {
     float h[3];
@@ -444,7 +453,9 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   for (int j = 0; j < n_acc; j += kAccelBatch) {
     const int nb = std::min(kAccelBatch, n_acc - j);
     LoadResampled ld;
-    ld.x = s->d_tim;
+    ld.D = reinterpret_cast<const float2*>(s->d_tim);
+    ld.n1 = p->n1;
+    ld.lg_n2 = s->lg_n2;
     for (int b = 0; b < nb; b++) ld.afs.v[b] = accel_fact(h_acc[j + b], s->prm.tsamp);
     ld.size = (double)size;
     {
@@ -513,7 +524,18 @@ long ps_search_fetch_peaks(ps_search* hs, ps_raw_peak* h_out, size_t max_out, vo
   return (long)count;
 }
 
-const float* ps_search_whitened_series(ps_search* s) { return s ? SS(s)->d_tim : nullptr; }
+// natural-order copy of the (internally transposed) whitened series; synchronous, diagnostics only
+const float* ps_search_whitened_series(ps_search* hs) {
+  Search* s = SS(hs);
+  if (!s) return nullptr;
+  const ps_fft_plan_t* p = s->plan;
+  if (!s->d_tim_nat && cudaMalloc(&s->d_tim_nat, sizeof(float) * s->prm.size) != cudaSuccess) return nullptr;
+  untranspose_pairs_kernel<<<ew_grid(p->M, 256, 2), 256>>>(reinterpret_cast<const float2*>(s->d_tim),
+                                                           reinterpret_cast<float2*>(s->d_tim_nat), p->M, p->n1, s->lg_n2);
+  g_launches.fetch_add(1);
+  if (cudaDeviceSynchronize() != cudaSuccess) return nullptr;
+  return s->d_tim_nat;
+}
 const float* ps_search_last_spectrum(ps_search* s) { return s ? SS(s)->last_spectrum : nullptr; }
 
 }  // extern "C"
