@@ -302,32 +302,77 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, Ff
   }
 }
 
+// ---- TMA bulk copy (cp.async.bulk) + mbarrier helpers: one thread moves a whole contiguous tile
+// global -> shared asynchronously; no LSU instructions, no registers, completion on an mbarrier.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Pass 2: a work item's operands are one contiguous 64 KiB tile of the tiled inter-pass buffer, so
+// thread 0 fetches the NEXT tile with a single bulk copy into a staging buffer while the current
+// tile is transformed (issued once every thread has taken its operands out of the staging buffer).
 template <int R3, bool INV, class Storer>
 __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer st, FftTables t, int n1, int n2, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
-  extern __shared__ float smem[];
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) unsigned long long bar;
   const int ntiles = n1 / C::F;
   const int nwork = ntiles * nbatch;
-  const size_t M = (size_t)n1 * n2;
+  const size_t tile_elems = (size_t)n2 * C::F;  // complex words per tile, contiguous in Yt
+  constexpr unsigned kTileBytes = sizeof(cf) * 16 * C::THREADS;
+  cf* stage = reinterpret_cast<cf*>(smem + C::SMEM_WORDS);
   int work = blockIdx.x;
   if (work >= nwork) return;
-  cf v[16];
-  {
-    LoadPass2 ld{Yt + (size_t)(work / ntiles) * M, n1, (work % ntiles) * C::F, n2, C::F};
-    load_operands<C>(ld, v);
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_proxy_async();
+    mbar_expect_tx(&bar, kTileBytes);
+    bulk_g2s(stage, Yt + (size_t)work * tile_elems, kTileBytes, &bar);
   }
+  __syncthreads();
+  unsigned parity = 0;
   for (; work < nwork; work += gridDim.x) {
     const int b = work / ntiles, tile = work - b * ntiles;
     st.begin(b, tile * C::F, n1);
+    mbar_wait(&bar, parity);
+    parity ^= 1u;
+    cf v[16];
+#pragma unroll
+    for (int a = 0; a < 16; a++) v[a] = stage[a * C::THREADS + threadIdx.x];
     C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
-    __syncthreads();
+    __syncthreads();  // E1 complete; every thread has taken its operands out of the staging buffer
+    const int next = work + gridDim.x;
+    if (threadIdx.x == 0 && next < nwork) {
+      fence_proxy_async();
+      mbar_expect_tx(&bar, kTileBytes);
+      bulk_g2s(stage, Yt + (size_t)next * tile_elems, kTileBytes, &bar);
+    }
     C::phaseB(threadIdx.x, smem, t.W4096, st);
     __syncthreads();
-    const int next = work + gridDim.x;
-    if (next < nwork) {
-      LoadPass2 ld{Yt + (size_t)(next / ntiles) * M, n1, (next % ntiles) * C::F, n2, C::F};
-      load_operands<C>(ld, v);
-    }
     C::phaseC(threadIdx.x, smem, st);
   }
 }
@@ -365,7 +410,7 @@ inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass2_kernel<R3, INV, Storer>;
   static bool done[64] = {};
-  const size_t smem = C::SMEM_BYTES;
+  const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;  // exchange buffers + TMA staging tile
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
   k<<<fft_grid(p->n1 / C::F * nbatch), C::THREADS, smem, st>>>(p->Yt, stor, p->tables(), p->n1, p->n2, nbatch);
