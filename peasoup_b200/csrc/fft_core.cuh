@@ -195,11 +195,18 @@ struct CtaFft {
 
   // v[a] = element a*G + u of FFT f, already in registers
   PS_HD static void phaseA_regs(int t, float* s, const cf* W4096, cf* v) {
-    const int f = t % F, u = t / F;
-    cf* e1 = reinterpret_cast<cf*>(s);
+    phaseA_compute(t, W4096, v);
+    phaseA_write(t, s, v);
+  }
+  PS_HD static void phaseA_compute(int t, const cf* W4096, cf* v) {
+    const int u = t / F;
     dft16<INV>(v);
     cf w1 = ldg_cf(&W4096[u * (4096 / N)]);
     twiddle_powers16(v, dirw<INV>(w1));
+  }
+  PS_HD static void phaseA_write(int t, float* s, const cf* v) {
+    const int f = t % F, u = t / F;
+    cf* e1 = reinterpret_cast<cf*>(s);
 #pragma unroll
     for (int ka = 0; ka < 16; ka++) e1[(ka * G + u) * F + f] = v[ka];
   }

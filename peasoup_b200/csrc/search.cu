@@ -19,7 +19,7 @@
 namespace ps {
 
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
-constexpr int kAccelBatch = 2;  // acceleration trials per launch (fills the tail of the 148-SM waves)
+constexpr int kAccelBatch = 4;  // acceleration trials per launch (fills the tail of the 148-SM waves; measured 1: 94, 2: 74, 4: 68 us/trial)
 void plan_destroy(ps_fft_plan_t* p);
 
 struct LevelRanges {
@@ -453,8 +453,12 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   unsigned size = s->prm.size;
   int rc;
   PeakSink sink{s->d_peaks, s->d_count, s->cap};
-  for (int j = 0; j < n_acc; j += kAccelBatch) {
-    const int nb = std::min(kAccelBatch, n_acc - j);
+  static const int env_batch = getenv("PS_BATCH") ? std::max(1, std::min(kAccelBatch, atoi(getenv("PS_BATCH")))) : kAccelBatch;
+  // TMA tensor-map tile stores (fft_pass*_tma_kernel) measured ~3 % slower than plain stores on
+  // this workload (the passes are issue-bound, not store-latency-bound): opt-in via PS_TMA=1
+  static const bool env_tma = getenv("PS_TMA") ? atoi(getenv("PS_TMA")) != 0 : false;
+  for (int j = 0; j < n_acc; j += env_batch) {
+    const int nb = std::min(env_batch, n_acc - j);
     LoadResampled ld;
     ld.D = reinterpret_cast<const float2*>(s->d_tim);
     ld.n1 = p->n1;
@@ -467,9 +471,14 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
       ld.max_shift = (float)(amax * 0.25 * (double)size * (double)size * 1.001);  // |i(i-N)| <= N^2/4
       ld.max_step = (float)(amax * (double)size * 1.001);                         // |d/di| <= N
     }
-    if ((rc = launch_pass1<false>(p, ld, st, nb))) return rc;
-    StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
-    if ((rc = launch_pass2<false>(p, sn, st, nb))) return rc;
+    if (p->has_tma && env_tma) {
+      if ((rc = launch_pass1_tma<false>(p, ld, st, nb))) return rc;
+      if ((rc = launch_pass2_tma<false>(p, st, nb))) return rc;
+    } else {
+      if ((rc = launch_pass1<false>(p, ld, st, nb))) return rc;
+      StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
+      if ((rc = launch_pass2<false>(p, sn, st, nb))) return rc;
+    }
     dim3 g1(ew_grid(p->M / 4, 256, 1), nb);
     spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
                                         (float)size, p->TC, p->TD,
@@ -490,7 +499,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
 #undef PS_HP
     PS_LAUNCHED("harmonic_peaks_kernel");
   }
-  s->last_spectrum = s->d_pbatch + (size_t)((n_acc - 1) % kAccelBatch) * s->pstride;
+  s->last_spectrum = s->d_pbatch + (size_t)((n_acc - 1) % env_batch) * s->pstride;
   return PS_OK;
 }
 

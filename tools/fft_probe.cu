@@ -71,6 +71,58 @@ float run(const char* name, const cf* Yt, Storer st, FftTables t, int n1, int n2
   return ms;
 }
 
+template <int MODE, class Storer>
+__global__ void __launch_bounds__(512, 1) probe1_kernel(LoadResampled ld, Storer st0, cf* Yt, FftTables t, int n1, int n2, int nbatch, int tw2) {
+  using C = psfft::CtaFft<8, false>;
+  extern __shared__ float smem[];
+  const int ntiles = n2 / C::F, nwork = ntiles * nbatch;
+  const size_t M = (size_t)n1 * n2;
+  int work = blockIdx.x;
+  if (work >= nwork) return;
+  cf v[16];
+  auto load = [&](int w) {
+    if (MODE == 1) {
+#pragma unroll
+      for (int a = 0; a < 16; a++) v[a] = psfft::mk((float)(threadIdx.x + a + w), (float)(a * 3 - w));
+    } else {
+      ld.begin(w / ntiles, (w % ntiles) * C::F, n2);
+      load_operands<C>(ld, v);
+    }
+  };
+  load(work);
+  for (; work < nwork; work += gridDim.x) {
+    const int b = work / ntiles, tile = work - b * ntiles;
+    StorePass1<false> st{Yt + (size_t)b * M, t, n1, tile * C::F, n2, tw2};
+    Storer sx = st0;
+    sx.begin(b, tile * C::F, n1);
+    C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
+    __syncthreads();
+    if (MODE == 2) C::phaseB(threadIdx.x, smem, t.W4096, sx); else C::phaseB(threadIdx.x, smem, t.W4096, st);
+    __syncthreads();
+    const int next = work + gridDim.x;
+    if (next < nwork) load(next);
+    if (MODE == 2) C::phaseC(threadIdx.x, smem, sx); else C::phaseC(threadIdx.x, smem, st);
+  }
+}
+
+template <int MODE>
+void run1(const char* name, LoadResampled ld, cf* Yt, FftTables t, int n1, int n2, int nbatch) {
+  using C = psfft::CtaFft<8, false>;
+  auto k = probe1_kernel<MODE, NullStore>;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);
+  NullStore ns{reinterpret_cast<float2*>(Yt), 0, 0};
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  for (int i = 0; i < 3; i++) k<<<148, 512, C::SMEM_BYTES>>>(ld, ns, Yt, t, n1, n2, nbatch, 4);
+  cudaEventRecord(e0);
+  const int reps = 20;
+  for (int i = 0; i < reps; i++) k<<<148, 512, C::SMEM_BYTES>>>(ld, ns, Yt, t, n1, n2, nbatch, 4);
+  cudaEventRecord(e1);
+  cudaEventSynchronize(e1);
+  float ms; cudaEventElapsedTime(&ms, e0, e1);
+  printf("pass1 %-10s %7.1f us per launch (%d trials)  err=%s\n", name, 1e3f * ms / reps, nbatch, cudaGetErrorString(cudaGetLastError()));
+}
+
 int main() {
   const int n1 = 2048, n2 = 2048, nbatch = 2;
   const size_t M = (size_t)n1 * n2;
@@ -93,5 +145,17 @@ int main() {
   run<3>("noA", Yt, sn, t, n1, n2, nbatch);
   run<4>("noB", Yt, sn, t, n1, n2, nbatch);
   run<5>("noC", Yt, sn, t, n1, n2, nbatch);
+  {
+    float* D; cudaMalloc(&D, sizeof(cf) * M); cudaMemset(D, 0, sizeof(cf) * M);
+    LoadResampled ld;
+    ld.D = reinterpret_cast<const float2*>(D);
+    double af = ((30.0f * 64e-6f) / (2 * 299792458.0));
+    for (int b = 0; b < 8; b++) ld.afs.v[b] = af * (b + 1) / 2;
+    ld.size = 2.0 * M; ld.n1 = n1; ld.lg_n2 = 11;
+    ld.max_shift = (float)(af * 4 * 0.25 * ld.size * ld.size); ld.max_step = (float)(af * 4 * ld.size);
+    run1<0>("full", ld, Yt, t, n1, n2, nbatch);
+    run1<1>("noload", ld, Yt, t, n1, n2, nbatch);
+    run1<2>("nostore", ld, Yt, t, n1, n2, nbatch);
+  }
   return 0;
 }
