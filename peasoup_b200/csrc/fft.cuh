@@ -152,8 +152,9 @@ struct LoadResampled {
 // C2R output storer writing the transposed pair layout LoadResampled reads: time pair e = k1 + n1*k2
 struct StoreTransposedPairs {
   float2* D;
-  int n1, r0;
-  int lg_n2;
+  int n1, r0;    // packed plan rows / first row of the tile (set by begin)
+  int lg_cols;   // log2 of the number of pair columns of the transposed layout
+  int col_len;   // pairs per column
   __device__ __forceinline__ void begin(int, int first, int n) {
     r0 = first;
     n1 = n;
@@ -163,7 +164,7 @@ struct StoreTransposedPairs {
 #pragma unroll
     for (int j = 0; j < R; j++) {
       const unsigned e = (unsigned)(r0 + f) + (unsigned)n1 * (unsigned)(k0 + stride * j);
-      D[(size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2)] = make_float2(v[j].x, v[j].y);
+      D[(size_t)(e & ((1u << lg_cols) - 1u)) * col_len + (e >> lg_cols)] = make_float2(v[j].x, v[j].y);
     }
   }
 };

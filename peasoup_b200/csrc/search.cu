@@ -14,7 +14,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <vector>
-#include "fft.cuh"
+#include "rfft.cuh"
 
 namespace ps {
 
@@ -272,7 +272,11 @@ struct Search {
   unsigned nbins = 0;
   float* d_tim = nullptr;      // whitened series as size/2 complex pairs, TRANSPOSED (see LoadResampled)
   float* d_tim_nat = nullptr;  // natural-order copy, made on request (ps_search_whitened_series)
-  int lg_n2 = 0;
+  int lg_n2 = 0;    // log2(pair columns) of the transposed whitened series
+  int col_len = 0;  // pairs per column
+  bool fused = false;  // real-input two-kernel path (rfft.cuh) available for this size
+  RfftGeom geom;
+  cf* d_yr = nullptr;  // its tiled inter-pass buffer (kAccelBatch transforms)
   float2* d_X = nullptr;       // nbins complex
   float* d_pspec = nullptr;    // nbins
   float* d_median = nullptr;   // nbins
@@ -300,7 +304,7 @@ static void free_search(Search* s) {
   plan_destroy(s->plan);
   cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
-  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch);
+  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch); cudaFree(s->d_yr);
   delete s;
 }
 
@@ -344,6 +348,15 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   unsigned size = p->size;
   s->nbins = size / 2 + 1;
   while ((1 << s->lg_n2) < s->plan->n2) s->lg_n2++;
+  s->col_len = s->plan->n1;
+  // Experimental two-kernel real-input path (rfft.cuh): parity-green, but measured slower than the
+  // packed transform + spectrum_kernel at 2^23 (96 vs 68 us/trial: its 4096-point column pass and
+  // 16-byte spectrum stores cost more than the packed spectrum round trip saves) -> opt-in only.
+  s->fused = rfft_geometry(size, &s->geom) && getenv("PS_FUSED") && atoi(getenv("PS_FUSED")) == 1;
+  if (s->fused) {  // the whitened series is transposed for the fused path's columns instead
+    s->lg_n2 = s->geom.lgC;
+    s->col_len = s->geom.L1;
+  }
   float tobs = size * p->tsamp;            // pipeline_multi.cu:118
   float bin_width = 1.0 / tobs;            // :119
   s->bin_width_f = bin_width;
@@ -375,6 +388,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (e == cudaSuccess) e = cudaMalloc(&s->d_peaks, sizeof(ps_raw_peak) * (size_t)s->cap);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_count, sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * kAccelBatch);
+  if (e == cudaSuccess && s->fused) e = cudaMalloc(&s->d_yr, sizeof(cf) * s->geom.ystride * kAccelBatch);
   if (e == cudaSuccess) e = cudaMemset(s->d_count, 0, sizeof(unsigned));
   if (e != cudaSuccess) {
     free_search(s);
@@ -433,7 +447,7 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   if ((rc = launch_stats(s->d_pspec, s->nbins, s->d_partials, s->d_stats, st))) return rc;
   LoadC2RPre lc{s->d_X, p->M, p->n2, 0};
   if ((rc = launch_pass1<true>(p, lc, st))) return rc;
-  StoreTransposedPairs so{reinterpret_cast<float2*>(s->d_tim), 0, 0, s->lg_n2};
+  StoreTransposedPairs so{reinterpret_cast<float2*>(s->d_tim), 0, 0, s->lg_n2, s->col_len};
   if ((rc = launch_pass2<true>(p, so, st))) return rc;
   if (h_mean || h_std) {
     float h[3];
@@ -461,7 +475,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     const int nb = std::min(env_batch, n_acc - j);
     LoadResampled ld;
     ld.D = reinterpret_cast<const float2*>(s->d_tim);
-    ld.n1 = p->n1;
+    ld.n1 = s->col_len;
     ld.lg_n2 = s->lg_n2;
     for (int b = 0; b < nb; b++) ld.afs.v[b] = accel_fact(h_acc[j + b], s->prm.tsamp);
     ld.size = (double)size;
@@ -471,7 +485,10 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
       ld.max_shift = (float)(amax * 0.25 * (double)size * (double)size * 1.001);  // |i(i-N)| <= N^2/4
       ld.max_step = (float)(amax * (double)size * 1.001);                         // |d/di| <= N
     }
-    if (p->has_tma && env_tma) {
+    if (s->fused) {
+      if ((rc = launch_rfft_pass1(p, s->geom, ld, s->d_yr, st, nb))) return rc;
+      if ((rc = launch_rfft_pass2(p, s->geom, s->d_yr, s->d_pbatch, s->pstride, s->d_stats, (float)size, st, nb))) return rc;
+    } else if (p->has_tma && env_tma) {
       if ((rc = launch_pass1_tma<false>(p, ld, st, nb))) return rc;
       if ((rc = launch_pass2_tma<false>(p, st, nb))) return rc;
     } else {
@@ -479,11 +496,13 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
       StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
       if ((rc = launch_pass2<false>(p, sn, st, nb))) return rc;
     }
-    dim3 g1(ew_grid(p->M / 4, 256, 1), nb);
-    spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
-                                        (float)size, p->TC, p->TD,
-                                        make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
-    PS_LAUNCHED("spectrum_kernel");
+    if (!s->fused) {
+      dim3 g1(ew_grid(p->M / 4, 256, 1), nb);
+      spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
+                                          (float)size, p->TC, p->TD,
+                                          make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
+      PS_LAUNCHED("spectrum_kernel");
+    }
     dim3 g2((((unsigned)s->nbins + 511) / 512 + 3) / 4, nb);
 #define PS_HP(NF)                                                                                                \
   harmonic_peaks_kernel<NF><<<g2, 128, 0, st>>>(s->d_pbatch, (int)s->nbins, s->pstride, s->ranges, s->scales,   \
@@ -543,7 +562,7 @@ const float* ps_search_whitened_series(ps_search* hs) {
   const ps_fft_plan_t* p = s->plan;
   if (!s->d_tim_nat && cudaMalloc(&s->d_tim_nat, sizeof(float) * s->prm.size) != cudaSuccess) return nullptr;
   untranspose_pairs_kernel<<<ew_grid(p->M, 256, 2), 256>>>(reinterpret_cast<const float2*>(s->d_tim),
-                                                           reinterpret_cast<float2*>(s->d_tim_nat), p->M, p->n1, s->lg_n2);
+                                                           reinterpret_cast<float2*>(s->d_tim_nat), p->M, s->col_len, s->lg_n2);
   g_launches.fetch_add(1);
   if (cudaDeviceSynchronize() != cudaSuccess) return nullptr;
   return s->d_tim_nat;

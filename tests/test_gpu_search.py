@@ -55,7 +55,9 @@ def compare_candidates(got, want, cfg, threshold=9.0):
 
 
 # ------------------------------------------------------------------ stage-level: whitening + spectra
-@pytest.mark.parametrize("size,nsamps,zap", [(1 << 17, (1 << 17) + 300, False), (1 << 17, 100000, True), (1 << 18, 1 << 18, True)])
+@pytest.mark.parametrize("size,nsamps,zap", [(1 << 17, (1 << 17) + 300, False), (1 << 17, 100000, True), (1 << 18, 1 << 18, True),
+                                             (1 << 20, (1 << 20) + 100, True), (1 << 21, (1 << 21) - 777, False),
+                                             (1 << 22, 1 << 22, False)])
 def test_whiten_and_spectrum_vs_oracle(lib, oracle, size, nsamps, zap):
     tsamp = 64e-6
     trial = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=20.0, amp=8.0)[0]
@@ -82,7 +84,26 @@ def test_whiten_and_spectrum_vs_oracle(lib, oracle, size, nsamps, zap):
     s.close()
 
 
-@pytest.mark.parametrize("size", [1 << 17, 1 << 19])
+@pytest.mark.parametrize("size", [1 << 20, 1 << 21])
+def test_experimental_real_input_path_vs_oracle(lib, oracle, size, monkeypatch):
+    """PS_FUSED=1 selects the two-kernel real-input transform (rfft.cuh) when the handle is created."""
+    monkeypatch.setenv("PS_FUSED", "1")
+    tsamp = 64e-6
+    trial = make_trials(1, size, size, tsamp=tsamp, a_inj=20.0, amp=8.0)[0]
+    cfg = oracle.SearchConfig(size, tsamp)
+    s = pb.Search(make_search_params(size, size, tsamp))
+    s.whiten(torch.from_numpy(trial).cuda())
+    tim, wmean, wstd = oracle.whiten(trial, cfg)
+    for acc in (0.0, 20.0, -47.3):
+        s.reset_peaks()
+        s.accel_batch([acc])
+        p = dev_f32(s.last_spectrum_ptr(), cfg.nbins)
+        want = oracle.accel_spectrum(tim, acc, wmean, wstd, cfg)
+        assert np.abs(p - want).max() < 20 * SPEC_TOL and np.sqrt(((p - want) ** 2).mean()) < SPEC_TOL
+    s.close()
+
+
+@pytest.mark.parametrize("size", [1 << 17, 1 << 19, 1 << 20])
 def test_raw_peaks_vs_oracle(lib, oracle, size):
     tsamp = 64e-6
     thresh = 6.0  # low threshold: thousands of peaks exercise the compaction
