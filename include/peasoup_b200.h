@@ -218,6 +218,36 @@ long ps_pipeline_run(ps_pipeline* h, const unsigned char* h_trials, const float*
                      long max_out, unsigned long long* trials_done);
 void ps_pipeline_close(ps_pipeline* h);
 
+/* ---------------- the stages either side of the hot path ---------- */
+/* dedisp_generate_dm_list as called at dedisperser.hpp:54-62 (external dedisp library, restated).
+ * dt seconds, ti = pulse width (us), f0/df MHz.  Returns the list length (out may be NULL). */
+int ps_dedisp_generate_dm_list(float dm_start, float dm_end, float dt, float ti, float f0, float df,
+                               int nchans, float tol, float* out, int max_out);
+/* dedisp_get_max_delay (dedisperser.hpp:100). */
+long ps_dedisp_max_delay(const float* h_dm_list, int ndm, int nchans, float dt, float f0, float df);
+/* dedisp_execute with 8-bit output (dedisperser.hpp:98-113): h_in = packed filterbank
+ * [nsamps][nchans] (nbits 1/2/4/8), h_out = [ndm][nout] with nout = nsamps - max_delay.  Host
+ * pointers; synchronous. */
+int ps_dedisperse(const unsigned char* h_in, size_t nsamps, int nchans, int nbits, float dt, float f0,
+                  float df, const float* h_dm_list, int ndm, const int* h_killmask,
+                  unsigned char* h_out, size_t nout);
+
+typedef struct {
+  ps_pipeline_params pipe;  /* search.size = --fft_size (0: prev_power_of_two); nsamps, tsamp, cfreq, foff come from the file */
+  float dm_start, dm_end, dm_tol, dm_pulse_width; /* --dm_start --dm_end --dm_tol --dm_pulse_width */
+  int limit;                /* --limit (< 0: no limit) */
+  int nworkers, device0;    /* -t */
+  const char* killfile;     /* -k, may be NULL */
+  const char* zapfile;      /* -z, may be NULL */
+  const char* outdir;       /* -o: candidates.peasoup + overview.xml are written when non-NULL */
+} ps_filterbank_params;
+/* main() of src/pipeline_multi.cu:262-419 without folding (--npdmp, row f3): read the SIGPROC
+ * filterbank, dedisperse, search every DM trial, DM + harmonic distillation, scoring, --limit.
+ * out: final candidates flattened depth-first (is_top = 1 starts a candidate).  seconds4
+ * (optional): reading, dedispersion, searching, total. */
+long ps_search_filterbank(const char* filename, const ps_filterbank_params* p, ps_candidate* out,
+                          long max_out, float* dm_list_out, int max_dm, int* ndm_out, double* seconds4);
+
 /* Diagnostics of the last ps_pipeline_search call of this process, summed over workers:
  * seconds spent queueing device work, waiting for the device, and in host-side clustering +
  * distillation, then the number of raw above-threshold bins fetched. */

@@ -420,3 +420,66 @@ def parse_overview_xml(path):
                                          txt[txt.index("<acceleration_trials"):txt.index("</acceleration_trials>")])]
     params = dict(re.findall(r"<(\w+)>([^<]*)</\1>", txt[txt.index("<search_parameters>"):txt.index("</search_parameters>")]))
     return dict(dm_list=np.array(dms, f32), acc_list=np.array(accs, f32), params=params)
+
+
+# ------------------------------------------------------------------ after the workers join (row f2)
+def _tree(recs):
+    """flattened records (is_top marks an entry, associates follow) -> list of [rec, assoc-list]"""
+    out = []
+    for r in recs:
+        node = [r.copy(), []]
+        if r["is_top"] or not out:
+            out.append(node)
+        else:
+            out[-1][1].append(node)
+    return out
+
+
+def _flatten_tree(nodes, top=True):
+    recs = []
+    for rec, assoc in nodes:
+        r = rec.copy()
+        r["is_top"] = 1 if top else 0
+        recs.append(r)
+        recs.extend(_flatten_tree(assoc, False))
+    return recs
+
+
+def _distill_tree(nodes, cond):
+    """BaseDistiller::distill (distiller.hpp:26-59) on candidates that carry associates."""
+    import copy
+    nodes = sorted(nodes, key=lambda n: -float(n[0]["snr"]))  # stable; std::sort may order ties differently
+    unique = [True] * len(nodes)
+    for i in range(len(nodes)):
+        if not unique[i]:
+            continue
+        for j in range(i + 1, len(nodes)):
+            for _ in range(cond(nodes[i][0], nodes[j][0])):
+                nodes[i][1].append(copy.deepcopy(nodes[j]))
+                unique[j] = False
+    return [n for n, u in zip(nodes, unique) if u]
+
+
+def finalise(recs, freq_tol=1e-4, max_harm=16, limit=1000):
+    """pipeline_multi.cu:353-365,390-391: DMDistiller(tol, true), HarmonicDistiller(tol, max_harm,
+    true, false), truncation to --limit (scores are not part of the record)."""
+    upper = float(f32(1) + f32(freq_tol))
+    lower = float(f32(1) - f32(freq_tol))
+
+    def dm_cond(a, b):
+        ratio = float(b["freq"]) / float(a["freq"])
+        return 1 if lower < ratio < upper else 0
+
+    def harm_cond(a, b):
+        n = 0
+        for jj in range(1, int(max_harm) + 1):
+            ratio = float(b["freq"]) / (jj * float(a["freq"]))
+            if lower < ratio < upper:
+                n += 1
+        return n
+
+    nodes = _distill_tree(_tree(recs), dm_cond)
+    nodes = _distill_tree(nodes, harm_cond)
+    nodes = nodes[:limit]
+    flat = _flatten_tree(nodes)
+    return np.array(flat, CAND_DTYPE) if flat else np.zeros(0, CAND_DTYPE)

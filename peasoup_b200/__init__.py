@@ -32,6 +32,12 @@ class PipelineParams(C.Structure):
                 ("acc_pulse_width", C.c_float), ("cfreq", C.c_float), ("foff", C.c_float)]
 
 
+class FilterbankParams(C.Structure):
+    _fields_ = [("pipe", PipelineParams), ("dm_start", C.c_float), ("dm_end", C.c_float), ("dm_tol", C.c_float),
+                ("dm_pulse_width", C.c_float), ("limit", C.c_int), ("nworkers", C.c_int), ("device0", C.c_int),
+                ("killfile", C.c_char_p), ("zapfile", C.c_char_p), ("outdir", C.c_char_p)]
+
+
 class RawPeak(C.Structure):
     _fields_ = [("acc_idx", C.c_int32), ("nh", C.c_int32), ("bin", C.c_int32), ("snr", C.c_float)]
 
@@ -52,7 +58,8 @@ SYMBOLS = [
     "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks",
     "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
     "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
-    "ps_pipeline_run", "ps_pipeline_close",
+    "ps_pipeline_run", "ps_pipeline_close", "ps_dedisp_generate_dm_list", "ps_dedisp_max_delay",
+    "ps_dedisperse", "ps_search_filterbank",
     "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
 ]
 
@@ -102,6 +109,10 @@ def load() -> C.CDLL:
         "ps_pipeline_open": [C.POINTER(PipelineParams), vp, vp, i, i, i, C.POINTER(vp)],
         "ps_pipeline_run": [vp, vp, vp, i, i, vp, i, vp, C.c_long, C.POINTER(C.c_ulonglong)],
         "ps_pipeline_close": [vp],
+        "ps_dedisp_generate_dm_list": [f, f, f, f, f, f, i, f, vp, i],
+        "ps_dedisp_max_delay": [vp, i, i, f, f, f],
+        "ps_dedisperse": [vp, sz, i, i, f, f, f, vp, i, vp, vp, sz],
+        "ps_search_filterbank": [C.c_char_p, C.POINTER(FilterbankParams), vp, C.c_long, vp, i, C.POINTER(i), vp],
         "ps_accel_plan_generate": [f, f, f, f, u, f, f, f, f, vp, i],
         "ps_cluster_peaks": [vp, vp, i, i, vp, vp],
         "ps_peak_range": [i, d, i, f, f, C.POINTER(i), C.POINTER(i), C.POINTER(f)],
@@ -118,6 +129,8 @@ def load() -> C.CDLL:
     lib.ps_search_fetch_peaks.restype = C.c_long
     lib.ps_pipeline_search.restype = C.c_long
     lib.ps_pipeline_run.restype = C.c_long
+    lib.ps_search_filterbank.restype = C.c_long
+    lib.ps_dedisp_max_delay.restype = C.c_long
     lib.ps_pipeline_close.restype = None
     lib.ps_distill.restype = C.c_long
     lib.ps_search_whitened_series.restype = vp

@@ -1,0 +1,156 @@
+// dedisp.cu -- incoherent dedispersion of a SIGPROC filterbank to 8-bit DM trials: the step
+// immediately BEFORE the search hot path.
+//
+// The reference delegates this to the external `dedisp` library through
+// include/transforms/dedisperser.hpp:21-113 (dedisp_create_plan_multi, dedisp_generate_dm_list,
+// dedisp_set_killmask, dedisp_get_max_delay, dedisp_execute with out_nbits = 8).  dedisp is not in
+// the reference tree and has no pinned version; the arithmetic here restates its published
+// algorithm (delay table 4.15e3/dt*(f^-2 - f0^-2), round-to-nearest delays, channel sum, the
+// "2-bit HTRU" 8-bit output scaling) and is pinned end to end by the reference's golden
+// candidate file (tests/test_gpu_filterbank.py; the CPU oracle carries the same restatement).
+//
+// Two kernels: unpack_transpose_kernel turns the packed [time][channel] samples into one byte per
+// sample, channel-major, so that the dedispersion kernel's loads are contiguous in time;
+// dedisperse_kernel sums the delayed channels for (DM trial, time sample) and scales to 8 bits.
+#include <cmath>
+#include <vector>
+#include "common.cuh"
+
+namespace ps {
+
+// [nsamps][nchans] packed LSB-first  ->  U[chan][nsamps] bytes (killed channels zeroed)
+__global__ void __launch_bounds__(256) unpack_transpose_kernel(const unsigned char* __restrict__ in, unsigned char* __restrict__ U,
+                                                               const int* __restrict__ killmask, int nbits, int nchans,
+                                                               size_t nsamps) {
+  __shared__ unsigned char tile[32][33];
+  // tile of 32 channels x 32 samples
+  const int c0 = blockIdx.y * 32, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 8 rows of 32
+  const size_t t0 = (size_t)blockIdx.x * 32;
+  const int per = 8 / nbits, mask = (1 << nbits) - 1;
+  for (int r = ty; r < 32; r += 8) {
+    size_t t = t0 + r;
+    int c = c0 + tx;
+    unsigned char v = 0;
+    if (t < nsamps && c < nchans) {
+      size_t s = t * nchans + c;  // sample index
+      unsigned char byte = in[s / per];
+      v = (byte >> ((s % per) * nbits)) & mask;
+      if (killmask && !killmask[c]) v = 0;
+    }
+    tile[r][tx] = v;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    int c = c0 + r;
+    size_t t = t0 + tx;
+    if (t < nsamps && c < nchans) U[(size_t)c * nsamps + t] = tile[tx][r];
+  }
+}
+
+// out[dm][t] = scale( sum_c U[c][t + rn(dm * delay_table[c])] )
+__global__ void __launch_bounds__(256) dedisperse_kernel(const unsigned char* __restrict__ U, const float* __restrict__ delay_table,
+                                                         const float* __restrict__ dm_list, unsigned char* __restrict__ out,
+                                                         int nchans, size_t nsamps, size_t nout, float in_range, float factor) {
+  extern __shared__ unsigned delays[];
+  const int dm_idx = blockIdx.y;
+  const float dm = dm_list[dm_idx];
+  for (int c = threadIdx.x; c < nchans; c += blockDim.x) delays[c] = __float2uint_rn(__fmul_rn(dm, delay_table[c]));
+  __syncthreads();
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < nout; t += (size_t)gridDim.x * blockDim.x) {
+    unsigned sum = 0;
+    for (int c = 0; c < nchans; c++) sum += U[(size_t)c * nsamps + t + delays[c]];
+    // (float)sum * out_range / (in_range * nchans) * factor, clipped to [0, 255], truncated
+    float scaled = __fmul_rn(__fdiv_rn(__fmul_rn((float)sum, 255.0f), __fmul_rn(in_range, (float)nchans)), factor);
+    scaled = fminf(fmaxf(scaled, 0.0f), 255.0f);
+    out[(size_t)dm_idx * nout + t] = (unsigned char)scaled;
+  }
+}
+
+}  // namespace ps
+
+using namespace ps;
+
+extern "C" {
+
+int ps_dedisp_generate_dm_list(float dm_start, float dm_end, float dt, float ti, float f0, float df, int nchans, float tol,
+                               float* out, int max_out) {
+  // dedisp_generate_dm_list (called at dedisperser.hpp:57): published recurrence, double precision
+  double dtu = (double)dt * 1e6;
+  double f = ((double)f0 + ((nchans / 2) - 0.5) * (double)df) * 1e-3;
+  double tol2 = (double)tol * tol;
+  double a = 8.3 * df / (f * f * f);
+  double a2 = a * a;
+  double b2 = a2 * (double)(nchans * nchans / 16.0);
+  double c = (dtu * dtu + (double)ti * ti) * (tol2 - 1.0);
+  std::vector<double> dms;
+  dms.push_back(dm_start);
+  while (dms.back() < dm_end) {
+    double prev = dms.back(), prev2 = prev * prev;
+    double k = c + tol2 * a2 * prev2;
+    double dm = (b2 * prev + sqrt(-a2 * b2 * prev2 + (a2 + b2) * k)) / (a2 + b2);
+    dms.push_back(dm);
+    if (dms.size() > (1u << 22)) return invalid("ps_dedisp_generate_dm_list: DM list does not terminate");
+  }
+  for (size_t i = 0; i < dms.size() && (int)i < max_out; i++) out[i] = (float)dms[i];
+  return (int)dms.size();
+}
+
+// delay table and max delay as dedisp computes them (float arithmetic)
+static void delay_table_host(std::vector<float>& tab, int nchans, float dt, float f0, float df) {
+  tab.resize(nchans);
+  for (int c = 0; c < nchans; c++) {
+    float a = 1.f / (f0 + c * df);
+    float b = 1.f / f0;
+    tab[c] = (float)(4.15e3 / dt * (a * a - b * b));
+  }
+}
+
+long ps_dedisp_max_delay(const float* h_dm_list, int ndm, int nchans, float dt, float f0, float df) {
+  if (ndm <= 0 || nchans <= 0) return 0;
+  std::vector<float> tab;
+  delay_table_host(tab, nchans, dt, f0, df);
+  return (long)(h_dm_list[ndm - 1] * tab[nchans - 1] + 0.5f);
+}
+
+int ps_dedisperse(const unsigned char* h_in, size_t nsamps, int nchans, int nbits, float dt, float f0, float df,
+                  const float* h_dm_list, int ndm, const int* h_killmask, unsigned char* h_out, size_t nout) {
+  if (nbits != 1 && nbits != 2 && nbits != 4 && nbits != 8) return invalid("ps_dedisperse: nbits must be 1, 2, 4 or 8");
+  if (ndm <= 0 || nchans <= 0 || !nsamps) return invalid("ps_dedisperse: empty input");
+  long max_delay = ps_dedisp_max_delay(h_dm_list, ndm, nchans, dt, f0, df);
+  if ((size_t)max_delay >= nsamps || nout != nsamps - (size_t)max_delay)
+    return invalid("ps_dedisperse: nout must equal nsamps - max_delay");
+  std::vector<float> tab;
+  delay_table_host(tab, nchans, dt, f0, df);
+  size_t in_bytes = nsamps * nchans * nbits / 8;
+  unsigned char *d_in = 0, *d_U = 0, *d_out = 0;
+  float *d_tab = 0, *d_dm = 0;
+  int* d_kill = 0;
+  cudaError_t e = cudaMalloc(&d_in, in_bytes);
+  if (e == cudaSuccess) e = cudaMalloc(&d_U, (size_t)nchans * nsamps);
+  if (e == cudaSuccess) e = cudaMalloc(&d_out, (size_t)ndm * nout);
+  if (e == cudaSuccess) e = cudaMalloc(&d_tab, sizeof(float) * nchans);
+  if (e == cudaSuccess) e = cudaMalloc(&d_dm, sizeof(float) * ndm);
+  if (e == cudaSuccess && h_killmask) e = cudaMalloc(&d_kill, sizeof(int) * nchans);
+  if (e == cudaSuccess) e = cudaMemcpy(d_in, h_in, in_bytes, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_tab, tab.data(), sizeof(float) * nchans, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_dm, h_dm_list, sizeof(float) * ndm, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && h_killmask) e = cudaMemcpy(d_kill, h_killmask, sizeof(int) * nchans, cudaMemcpyHostToDevice);
+  int rc = PS_OK;
+  if (e == cudaSuccess) {
+    dim3 g1((unsigned)((nsamps + 31) / 32), (unsigned)((nchans + 31) / 32));
+    unpack_transpose_kernel<<<g1, 256>>>(d_in, d_U, d_kill, nbits, nchans, nsamps);
+    g_launches.fetch_add(1);
+    dim3 g2((unsigned)std::min<size_t>((nout + 255) / 256, 148 * 8), (unsigned)ndm);
+    float in_range = (float)((1 << nbits) - 1);
+    float factor = ((3.f * 1024.f) / 255.f) / 16.f;
+    dedisperse_kernel<<<g2, 256, sizeof(unsigned) * nchans>>>(d_U, d_tab, d_dm, d_out, nchans, nsamps, nout, in_range, factor);
+    g_launches.fetch_add(1);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpy(h_out, d_out, (size_t)ndm * nout, cudaMemcpyDeviceToHost);
+  }
+  if (e != cudaSuccess) rc = cuda_fail(e, "ps_dedisperse");
+  cudaFree(d_in); cudaFree(d_U); cudaFree(d_out); cudaFree(d_tab); cudaFree(d_dm); cudaFree(d_kill);
+  return rc;
+}
+
+}  // extern "C"

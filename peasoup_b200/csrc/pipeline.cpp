@@ -3,7 +3,8 @@
 #include <exception>
 #include <string>
 #include <thread>
-#include "../../include/peasoup_b200/pipeline.hpp"
+#include <chrono>
+#include "../../include/peasoup_b200/postprocess.hpp"
 
 namespace ps {
 void set_error(const std::string& msg);
@@ -156,6 +157,95 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
   long n = ps_pipeline_run(h, h_trials, h_dm_list, ndm, dm_idx_offset, h_acc_explicit, n_acc_explicit, out, max_out, trials_done);
   ps_pipeline_close(h);
   return n;
+}
+
+// main() of src/pipeline_multi.cu:262-419 without the folding step (row f3)
+long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, ps_candidate* out, long max_out,
+                          float* dm_list_out, int max_dm, int* ndm_out, double* seconds4) {
+  typedef std::chrono::steady_clock clk;
+  auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+  try {
+    if (!filename || !fp) ErrorChecker::throw_error("ps_search_filterbank: null argument");
+    clk::time_point t0 = clk::now();
+    SigprocFilterbank filobj(filename);
+    clk::time_point t1 = clk::now();
+    const int nworkers = fp->nworkers < 1 ? 1 : fp->nworkers;
+    Dedisperser dedisperser(filobj, nworkers);
+    if (fp->killfile && fp->killfile[0]) dedisperser.set_killmask(std::string(fp->killfile));
+    dedisperser.generate_dm_list(fp->dm_start, fp->dm_end, fp->dm_pulse_width, fp->dm_tol);
+    std::vector<float> dm_list = dedisperser.get_dm_list();
+    DispersionTrials<unsigned char> trials = dedisperser.dedisperse();
+    clk::time_point t2 = clk::now();
+    if (ndm_out) *ndm_out = (int)dm_list.size();
+    for (size_t i = 0; dm_list_out && i < dm_list.size() && (int)i < max_dm; i++) dm_list_out[i] = dm_list[i];
+
+    ps_pipeline_params pp = fp->pipe;
+    unsigned size = pp.search.size ? pp.search.size : Utils::prev_power_of_two(filobj.get_nsamps());  // :326-331
+    pp.search.size = size;
+    pp.search.nsamps = trials.get_nsamps();
+    pp.search.tsamp = trials.get_tsamp();
+    pp.cfreq = filobj.get_cfreq();
+    pp.foff = filobj.get_foff();
+    std::vector<float> zf, zw;
+    if (fp->zapfile && fp->zapfile[0]) Zapper::parse(std::string(fp->zapfile), zf, zw);
+    ps_pipeline* h = 0;
+    if (ps_pipeline_open(&pp, zf.empty() ? 0 : &zf[0], zw.empty() ? 0 : &zw[0], (int)zf.size(), fp->device0, nworkers, &h))
+      ErrorChecker::throw_error(ps_last_error());
+    std::vector<ps_candidate> flat(1 << 20);
+    long n = ps_pipeline_run(h, trials.get_data(), &dm_list[0], (int)dm_list.size(), 0, 0, 0, flat.data(), (long)flat.size(), 0);
+    ps_pipeline_close(h);
+    if (n < 0) ErrorChecker::throw_error(ps_last_error());
+    if (n > (long)flat.size()) ErrorChecker::throw_error("ps_search_filterbank: too many per-DM candidates");
+    clk::time_point t3 = clk::now();
+    // rebuild dm_cands (entries + their acceleration associates) from the flattened records
+    std::vector<Candidate> dm_cands;
+    for (long i = 0; i < n; i++) {
+      Candidate c(flat[i].dm, flat[i].dm_idx, flat[i].acc, flat[i].nh, flat[i].snr, flat[i].freq);
+      if (flat[i].is_top || dm_cands.empty())
+        dm_cands.push_back(c);
+      else
+        dm_cands.back().append(c);
+    }
+    CandidateScorer scorer(filobj.get_tsamp(), filobj.get_cfreq(), filobj.get_foff(), fabs(filobj.get_foff()) * filobj.get_nchans());
+    finalise_candidates(dm_cands, fp->pipe.freq_tol, (float)fp->pipe.max_harm, scorer, fp->limit);
+    clk::time_point t4 = clk::now();
+    if (fp->outdir && fp->outdir[0]) {
+      CandidateFileWriter cand_files(fp->outdir);
+      cand_files.write_binary(dm_cands, "candidates.peasoup");
+      OutputFileWriter stats;
+      stats.add_header(filobj.header);
+      std::map<std::string, std::string> prm;
+      auto put = [&](const char* k, double v) {
+        std::stringstream ss;
+        ss << std::setprecision(15) << v;
+        prm[k] = ss.str();
+      };
+      prm["infilename"] = filename;
+      put("size", size); put("dm_start", fp->dm_start); put("dm_end", fp->dm_end); put("dm_tol", fp->dm_tol);
+      put("dm_pulse_width", fp->dm_pulse_width); put("acc_start", pp.acc_start); put("acc_end", pp.acc_end);
+      put("acc_tol", pp.acc_tol); put("acc_pulse_width", pp.acc_pulse_width); put("nharmonics", pp.search.nharmonics);
+      put("min_snr", pp.search.min_snr); put("min_freq", pp.search.min_freq); put("max_freq", pp.search.max_freq);
+      put("max_harm", pp.max_harm); put("freq_tol", pp.freq_tol); put("limit", fp->limit);
+      stats.add_search_parameters(prm);
+      stats.add_dm_list(dm_list);
+      AccelerationPlan acc_plan(pp.acc_start, pp.acc_end, pp.acc_tol, pp.acc_pulse_width, size, pp.search.tsamp, pp.cfreq, pp.foff);
+      std::vector<float> acc_list;
+      acc_plan.generate_accel_list(0.0, acc_list);
+      stats.add_acc_list(acc_list);
+      stats.add_candidates(dm_cands, cand_files.byte_mapping);
+      std::map<std::string, double> tm;
+      tm["reading"] = secs(t0, t1); tm["dedispersion"] = secs(t1, t2); tm["searching"] = secs(t2, t3); tm["total"] = secs(t0, clk::now());
+      stats.add_timing_info(tm);
+      stats.to_file(std::string(fp->outdir) + "/overview.xml");
+    }
+    if (seconds4) {
+      seconds4[0] = secs(t0, t1); seconds4[1] = secs(t1, t2); seconds4[2] = secs(t2, t3); seconds4[3] = secs(t0, t4);
+    }
+    return flatten(dm_cands, out, max_out);
+  } catch (std::exception& e) {
+    ps::set_error(e.what());
+    return PS_ECUDA;
+  }
 }
 
 void ps_pipeline_profile(double* out4) {
