@@ -240,13 +240,42 @@ typedef struct {
   const char* killfile;     /* -k, may be NULL */
   const char* zapfile;      /* -z, may be NULL */
   const char* outdir;       /* -o: candidates.peasoup + overview.xml are written when non-NULL */
+  int npdmp;                /* --npdmp: fold and optimise this many top candidates (0: none) */
 } ps_filterbank_params;
-/* main() of src/pipeline_multi.cu:262-419 without folding (--npdmp, row f3): read the SIGPROC
- * filterbank, dedisperse, search every DM trial, DM + harmonic distillation, scoring, --limit.
+/* main() of src/pipeline_multi.cu:262-419: read the SIGPROC filterbank, dedisperse, search every
+ * DM trial, DM + harmonic distillation, scoring, folding of the top npdmp candidates
+ * (MultiFolder, folder.hpp:354-460; re-sorts by max(snr, folded_snr)), --limit.
  * out: final candidates flattened depth-first (is_top = 1 starts a candidate).  seconds4
- * (optional): reading, dedispersion, searching, total. */
+ * (optional): reading, dedispersion, searching, total.  folded_snr / opt_period and the FOLD
+ * blocks go to the output files; ps_fold_results_last() returns them to the caller. */
 long ps_search_filterbank(const char* filename, const ps_filterbank_params* p, ps_candidate* out,
                           long max_out, float* dm_list_out, int max_dm, int* ndm_out, double* seconds4);
+
+/* ---- folding ------------------------------------------------------------ */
+/* device_fold_timeseries (kernels.h; src/kernels.cu:597-653): d_out[nsubints][nbins], each bin the
+ * sum of its samples / (hits + 1).  Deterministic (sample order), see csrc/fold.cu. */
+int ps_fold_timeseries(const float* d_in, float* d_out, size_t nsamps, size_t nsubints, double period,
+                       double tsamp, int nbins, void* stream);
+typedef struct ps_fold_optimiser ps_fold_optimiser;
+typedef struct {
+  float opt_sn, sn1, sn2;   /* max(sn1, sn2) and the two estimators of folder.hpp:143-191 */
+  double opt_period;        /* folder.hpp:346 */
+  int opt_width, opt_bin, opt_shift;
+  unsigned argmax;          /* flat index into [template][drift][bin] */
+  float peak;               /* value at argmax */
+} ps_fold_result;
+/* FoldOptimiser::FoldOptimiser (folder.hpp:195-217): template and drift banks for nbins x nints. */
+int ps_fold_optimiser_create(unsigned nbins, unsigned nints, ps_fold_optimiser** out);
+void ps_fold_optimiser_destroy(ps_fold_optimiser* o);
+/* FoldOptimiser::optimise (folder.hpp:241-351): d_fold [nints][nbins] on the device; h_opt_fold
+ * [nints][nbins] and h_opt_prof [nbins] (host, optional) receive the optimised sub-integrations
+ * and profile.  Synchronises the stream. */
+int ps_fold_optimise(ps_fold_optimiser* o, const float* d_fold, double period, float tobs,
+                     float* h_opt_fold, float* h_opt_prof, ps_fold_result* res, void* stream);
+/* Fold results of the last ps_search_filterbank call of this process: for final candidate i
+ * (i < returned count) folded_snr[i], opt_period[i]; folds [count][16*64] when non-NULL (zeros for
+ * candidates that were not folded).  Returns the number of final candidates. */
+long ps_fold_results_last(float* folded_snr, double* opt_period, float* folds, long max_count);
 
 /* Diagnostics of the last ps_pipeline_search call of this process, summed over workers:
  * seconds spent queueing device work, waiting for the device, and in host-side clustering +

@@ -264,6 +264,11 @@ struct Candidate {
         is_adjacent(false), is_physical(false), ddm_count_ratio(0.f), ddm_snr_ratio(0.f), nbins(0), nints(0) {}
 
   void append(Candidate& other) { assoc.push_back(other); }
+  void set_fold(float* ar, int nbins_, int nints_) {  // candidates.hpp:69-76
+    nbins = nbins_;
+    nints = nints_;
+    fold.assign(ar, ar + (size_t)nbins_ * nints_);
+  }
   int count_assoc() {
     int count = 0;
     for (size_t i = 0; i < assoc.size(); i++) count += 1 + assoc[i].count_assoc();

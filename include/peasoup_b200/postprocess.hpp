@@ -2,8 +2,7 @@
 // (src/pipeline_multi.cu:353-416): DM and harmonic distillation of the merged
 // candidate list, candidate scoring (include/transforms/scorer.hpp), truncation to --limit and the
 // output files (include/utils/output_stats.hpp: candidates.peasoup binary + overview.xml).
-// Folding (--npdmp, row f3) is not implemented: folded_snr / opt_period stay 0 and no FOLD blocks
-// are written.
+// Folding (--npdmp, row f3) sits between scoring and truncation: folder.hpp.
 #pragma once
 #include <sys/stat.h>
 #include <cstdio>
@@ -12,6 +11,7 @@
 #include <iostream>
 #include <map>
 #include "filterbank.hpp"
+#include "folder.hpp"
 #include "pipeline.hpp"
 
 namespace peasoup_b200 {
@@ -58,18 +58,24 @@ class CandidateScorer {  // scorer.hpp:8-87
   }
 };
 
-// pipeline_multi.cu:353-369,390-391
-inline void finalise_candidates(std::vector<Candidate>& cands, float freq_tol, float max_harm, CandidateScorer& scorer, int limit) {
+// pipeline_multi.cu:353-391: distill, score, fold the top npdmp (re-sorting the list), truncate
+inline void finalise_candidates(std::vector<Candidate>& cands, float freq_tol, float max_harm, CandidateScorer& scorer, int limit,
+                                DispersionTrials<unsigned char>* trials = 0, int npdmp = 0) {
   DMDistiller dm_still(freq_tol, true);
   HarmonicDistiller harm_still(freq_tol, max_harm, true, false);
   cands = dm_still.distill(cands);
   cands = harm_still.distill(cands);
   scorer.score_all(cands);
+  if (trials && npdmp > 0) {
+    MultiFolder folder(cands, *trials);
+    folder.fold_n(npdmp);
+  }
   if (limit >= 0 && (size_t)limit < cands.size()) cands.resize(limit);
 }
 
-// candidates.peasoup (output_stats.hpp:238-268): per candidate int ndets + ndets 24-byte PODs
-// (the candidate itself first, then its associates depth-first)
+// candidates.peasoup (output_stats.hpp:238-268): per candidate an optional "FOLD" + nbins + nints +
+// nbins*nints floats block, then int ndets + ndets 24-byte PODs (the candidate itself first, then
+// its associates depth-first)
 class CandidateFileWriter {
  public:
   std::map<int, long> byte_mapping;
@@ -84,6 +90,12 @@ class CandidateFileWriter {
     if (!fo) ErrorChecker::throw_error("File " + path + " could not be opened: ");
     for (size_t i = 0; i < candidates.size(); i++) {
       byte_mapping[(int)i] = ftell(fo);
+      if (!candidates[i].fold.empty()) {
+        fputs("FOLD", fo);
+        fwrite(&candidates[i].nbins, sizeof(int), 1, fo);
+        fwrite(&candidates[i].nints, sizeof(int), 1, fo);
+        fwrite(&candidates[i].fold[0], sizeof(float), (size_t)candidates[i].nbins * candidates[i].nints, fo);
+      }
       std::vector<CandidatePOD> dets;
       candidates[i].collect_candidates(dets);
       int ndets = (int)dets.size();

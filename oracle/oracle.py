@@ -422,6 +422,15 @@ def parse_overview_xml(path):
     return dict(dm_list=np.array(dms, f32), acc_list=np.array(accs, f32), params=params)
 
 
+def parse_overview_candidates(path):
+    """<candidates> of overview.xml (output_stats.hpp:170-222) as a list of dicts of floats."""
+    txt = open(path, encoding="latin1").read()
+    out = []
+    for block in re.findall(r"<candidate id='\d+'>(.*?)</candidate>", txt, re.S):
+        out.append({k: float(v) for k, v in re.findall(r"<(\w+)>([^<]*)</\1>", block)})
+    return out
+
+
 # ------------------------------------------------------------------ after the workers join (row f2)
 def _tree(recs):
     """flattened records (is_top marks an entry, associates follow) -> list of [rec, assoc-list]"""

@@ -35,7 +35,13 @@ class PipelineParams(C.Structure):
 class FilterbankParams(C.Structure):
     _fields_ = [("pipe", PipelineParams), ("dm_start", C.c_float), ("dm_end", C.c_float), ("dm_tol", C.c_float),
                 ("dm_pulse_width", C.c_float), ("limit", C.c_int), ("nworkers", C.c_int), ("device0", C.c_int),
-                ("killfile", C.c_char_p), ("zapfile", C.c_char_p), ("outdir", C.c_char_p)]
+                ("killfile", C.c_char_p), ("zapfile", C.c_char_p), ("outdir", C.c_char_p), ("npdmp", C.c_int)]
+
+
+class FoldResult(C.Structure):
+    _fields_ = [("opt_sn", C.c_float), ("sn1", C.c_float), ("sn2", C.c_float), ("opt_period", C.c_double),
+                ("opt_width", C.c_int), ("opt_bin", C.c_int), ("opt_shift", C.c_int), ("argmax", C.c_uint),
+                ("peak", C.c_float)]
 
 
 class RawPeak(C.Structure):
@@ -59,7 +65,8 @@ SYMBOLS = [
     "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
     "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
     "ps_pipeline_run", "ps_pipeline_close", "ps_dedisp_generate_dm_list", "ps_dedisp_max_delay",
-    "ps_dedisperse", "ps_search_filterbank",
+    "ps_dedisperse", "ps_search_filterbank", "ps_fold_timeseries", "ps_fold_optimiser_create",
+    "ps_fold_optimiser_destroy", "ps_fold_optimise", "ps_fold_results_last",
     "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
 ]
 
@@ -113,6 +120,10 @@ def load() -> C.CDLL:
         "ps_dedisp_max_delay": [vp, i, i, f, f, f],
         "ps_dedisperse": [vp, sz, i, i, f, f, f, vp, i, vp, vp, sz],
         "ps_search_filterbank": [C.c_char_p, C.POINTER(FilterbankParams), vp, C.c_long, vp, i, C.POINTER(i), vp],
+        "ps_fold_timeseries": [vp, vp, sz, sz, d, d, i, vp],
+        "ps_fold_optimiser_create": [u, u, C.POINTER(vp)], "ps_fold_optimiser_destroy": [vp],
+        "ps_fold_optimise": [vp, vp, d, f, vp, vp, C.POINTER(FoldResult), vp],
+        "ps_fold_results_last": [vp, vp, vp, C.c_long],
         "ps_accel_plan_generate": [f, f, f, f, u, f, f, f, f, vp, i],
         "ps_cluster_peaks": [vp, vp, i, i, vp, vp],
         "ps_peak_range": [i, d, i, f, f, C.POINTER(i), C.POINTER(i), C.POINTER(f)],
@@ -133,6 +144,8 @@ def load() -> C.CDLL:
     lib.ps_dedisp_max_delay.restype = C.c_long
     lib.ps_pipeline_close.restype = None
     lib.ps_distill.restype = C.c_long
+    lib.ps_fold_results_last.restype = C.c_long
+    lib.ps_fold_optimiser_destroy.restype = None
     lib.ps_search_whitened_series.restype = vp
     lib.ps_search_last_spectrum.restype = vp
     lib.ps_peak_workspace_destroy.restype = None

@@ -159,7 +159,23 @@ long ps_pipeline_search(const ps_pipeline_params* p, const unsigned char* h_tria
   return n;
 }
 
-// main() of src/pipeline_multi.cu:262-419 without the folding step (row f3)
+// fold results of the last ps_search_filterbank call (ps_fold_results_last)
+static std::mutex g_fold_mu;
+static std::vector<float> g_fold_snr, g_fold_data;
+static std::vector<double> g_fold_period;
+
+long ps_fold_results_last(float* folded_snr, double* opt_period, float* folds, long max_count) {
+  std::lock_guard<std::mutex> lk(g_fold_mu);
+  long n = (long)g_fold_snr.size();
+  for (long i = 0; i < n && i < max_count; i++) {
+    if (folded_snr) folded_snr[i] = g_fold_snr[i];
+    if (opt_period) opt_period[i] = g_fold_period[i];
+    if (folds) memcpy(folds + i * 1024, &g_fold_data[i * 1024], sizeof(float) * 1024);
+  }
+  return n;
+}
+
+// main() of src/pipeline_multi.cu:262-419
 long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, ps_candidate* out, long max_out,
                           float* dm_list_out, int max_dm, int* ndm_out, double* seconds4) {
   typedef std::chrono::steady_clock clk;
@@ -207,8 +223,19 @@ long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, 
         dm_cands.back().append(c);
     }
     CandidateScorer scorer(filobj.get_tsamp(), filobj.get_cfreq(), filobj.get_foff(), fabs(filobj.get_foff()) * filobj.get_nchans());
-    finalise_candidates(dm_cands, fp->pipe.freq_tol, (float)fp->pipe.max_harm, scorer, fp->limit);
+    finalise_candidates(dm_cands, fp->pipe.freq_tol, (float)fp->pipe.max_harm, scorer, fp->limit, &trials, fp->npdmp);
     clk::time_point t4 = clk::now();
+    {
+      std::lock_guard<std::mutex> lk(g_fold_mu);
+      g_fold_snr.assign(dm_cands.size(), 0.f);
+      g_fold_period.assign(dm_cands.size(), 0.0);
+      g_fold_data.assign(dm_cands.size() * 1024, 0.f);
+      for (size_t i = 0; i < dm_cands.size(); i++) {
+        g_fold_snr[i] = dm_cands[i].folded_snr;
+        g_fold_period[i] = dm_cands[i].opt_period;
+        if (dm_cands[i].fold.size() == 1024) memcpy(&g_fold_data[i * 1024], &dm_cands[i].fold[0], sizeof(float) * 1024);
+      }
+    }
     if (fp->outdir && fp->outdir[0]) {
       CandidateFileWriter cand_files(fp->outdir);
       cand_files.write_binary(dm_cands, "candidates.peasoup");
@@ -225,7 +252,7 @@ long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, 
       put("dm_pulse_width", fp->dm_pulse_width); put("acc_start", pp.acc_start); put("acc_end", pp.acc_end);
       put("acc_tol", pp.acc_tol); put("acc_pulse_width", pp.acc_pulse_width); put("nharmonics", pp.search.nharmonics);
       put("min_snr", pp.search.min_snr); put("min_freq", pp.search.min_freq); put("max_freq", pp.search.max_freq);
-      put("max_harm", pp.max_harm); put("freq_tol", pp.freq_tol); put("limit", fp->limit);
+      put("max_harm", pp.max_harm); put("freq_tol", pp.freq_tol); put("limit", fp->limit); put("npdmp", fp->npdmp);
       stats.add_search_parameters(prm);
       stats.add_dm_list(dm_list);
       AccelerationPlan acc_plan(pp.acc_start, pp.acc_end, pp.acc_tol, pp.acc_pulse_width, size, pp.search.tsamp, pp.cfreq, pp.foff);

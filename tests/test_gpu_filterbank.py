@@ -61,11 +61,12 @@ def test_dedisperse_rejects_bad_arguments(lib):
     assert lib.ps_dedisperse(x.ctypes.data, 8, 8, 8, 64e-6, 1500.0, -1.0, d.ctypes.data, 1, None, x.ctypes.data, 7) == -2
 
 
-def run_tutorial(lib, outdir=None, limit=1000):
+def run_tutorial(lib, outdir=None, limit=1000, npdmp=0):
     prm = pb.FilterbankParams()
     prm.pipe = pb.PipelineParams(make_search_params(0, 0, 0.0, 4, 9.0), 1e-4, 16, -5.0, 5.0, 1.1, 64.0, 0.0, 0.0)
     prm.dm_start, prm.dm_end, prm.dm_tol, prm.dm_pulse_width = 0.0, 250.0, 1.1, 64.0
     prm.limit, prm.nworkers, prm.device0 = limit, 1, 0
+    prm.npdmp = npdmp
     prm.killfile, prm.zapfile = None, None
     prm.outdir = outdir.encode() if outdir else None
     out = np.zeros(1 << 18, CAND_DTYPE)
