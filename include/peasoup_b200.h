@@ -277,6 +277,24 @@ int ps_fold_optimise(ps_fold_optimiser* o, const float* d_fold, double period, f
  * candidates that were not folded).  Returns the number of final candidates. */
 long ps_fold_results_last(float* folded_snr, double* opt_period, float* folds, long max_count);
 
+/* ---- multibeam coincidencer ---------------------------------------------- */
+/* device_coincidencer (kernels.h; src/kernels.cu:1073-1100): d_arrays = DEVICE table of narrays
+ * device pointers; d_out[i] = 1 when fewer than beam_thresh arrays exceed thresh at i, else 0. */
+int ps_coincidencer(float* const* d_arrays, float* d_out, int narrays, size_t size, float thresh,
+                    int beam_thresh, void* stream);
+typedef struct {
+  float threshold;               /* --thresh (4.0) */
+  int beam_threshold;            /* --beam_thresh (4) */
+  const char* samp_outfilename;  /* --o: sample mask file, NULL or "" = do not write */
+  const char* spec_outfilename;  /* --o2: birdie list file, NULL or "" = do not write */
+} ps_coincidence_params;
+/* main() of src/coincidencer.cpp:122-214: every filterbank dedispersed at DM 0, whitened,
+ * normalised; sample mask [nsamps] and spectral mask [nsamps/2+1] by ps_coincidencer; files as the
+ * reference writes them.  Masks are also copied to h_samp_mask / h_spec_mask when non-NULL (up to
+ * max_samp / max_spec values).  Returns nsamps, or a negative error. */
+long ps_coincidence_files(const char* const* filenames, int nfiles, const ps_coincidence_params* p,
+                          float* h_samp_mask, size_t max_samp, float* h_spec_mask, size_t max_spec);
+
 /* Diagnostics of the last ps_pipeline_search call of this process, summed over workers:
  * seconds spent queueing device work, waiting for the device, and in host-side clustering +
  * distillation, then the number of raw above-threshold bins fetched. */

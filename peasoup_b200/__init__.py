@@ -38,6 +38,11 @@ class FilterbankParams(C.Structure):
                 ("killfile", C.c_char_p), ("zapfile", C.c_char_p), ("outdir", C.c_char_p), ("npdmp", C.c_int)]
 
 
+class CoincidenceParams(C.Structure):
+    _fields_ = [("threshold", C.c_float), ("beam_threshold", C.c_int), ("samp_outfilename", C.c_char_p),
+                ("spec_outfilename", C.c_char_p)]
+
+
 class FoldResult(C.Structure):
     _fields_ = [("opt_sn", C.c_float), ("sn1", C.c_float), ("sn2", C.c_float), ("opt_period", C.c_double),
                 ("opt_width", C.c_int), ("opt_bin", C.c_int), ("opt_shift", C.c_int), ("argmax", C.c_uint),
@@ -66,7 +71,8 @@ SYMBOLS = [
     "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
     "ps_pipeline_run", "ps_pipeline_close", "ps_dedisp_generate_dm_list", "ps_dedisp_max_delay",
     "ps_dedisperse", "ps_search_filterbank", "ps_fold_timeseries", "ps_fold_optimiser_create",
-    "ps_fold_optimiser_destroy", "ps_fold_optimise", "ps_fold_results_last",
+    "ps_fold_optimiser_destroy", "ps_fold_optimise", "ps_fold_results_last", "ps_coincidencer",
+    "ps_coincidence_files",
     "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
 ]
 
@@ -124,6 +130,8 @@ def load() -> C.CDLL:
         "ps_fold_optimiser_create": [u, u, C.POINTER(vp)], "ps_fold_optimiser_destroy": [vp],
         "ps_fold_optimise": [vp, vp, d, f, vp, vp, C.POINTER(FoldResult), vp],
         "ps_fold_results_last": [vp, vp, vp, C.c_long],
+        "ps_coincidencer": [vp, vp, i, sz, f, i, vp],
+        "ps_coincidence_files": [C.POINTER(C.c_char_p), i, C.POINTER(CoincidenceParams), vp, sz, vp, sz],
         "ps_accel_plan_generate": [f, f, f, f, u, f, f, f, f, vp, i],
         "ps_cluster_peaks": [vp, vp, i, i, vp, vp],
         "ps_peak_range": [i, d, i, f, f, C.POINTER(i), C.POINTER(i), C.POINTER(f)],
@@ -145,6 +153,7 @@ def load() -> C.CDLL:
     lib.ps_pipeline_close.restype = None
     lib.ps_distill.restype = C.c_long
     lib.ps_fold_results_last.restype = C.c_long
+    lib.ps_coincidence_files.restype = C.c_long
     lib.ps_fold_optimiser_destroy.restype = None
     lib.ps_search_whitened_series.restype = vp
     lib.ps_search_last_spectrum.restype = vp

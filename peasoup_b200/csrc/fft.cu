@@ -144,44 +144,72 @@ void plan_destroy(ps_fft_plan_t* p) {
 
 using namespace ps;
 
-struct ps_fft_plan {
-  ps_fft_plan_t impl;
-};
-
-extern "C" {
-
-int ps_fft_plan_create(unsigned n, ps_fft_plan** out) {
-  ps_fft_plan_t* p = nullptr;
-  int rc = plan_create(n, &p, 1);
-  if (rc) return rc;
-  *out = reinterpret_cast<ps_fft_plan*>(p);
-  return PS_OK;
-}
-
-void ps_fft_plan_destroy(ps_fft_plan* plan) { plan_destroy(reinterpret_cast<ps_fft_plan_t*>(plan)); }
-
-int ps_fft_r2c(ps_fft_plan* plan, const float* d_in, ps_complex* d_out, void* stream) {
-  if (!plan) return invalid("ps_fft_r2c: null plan");
-  const ps_fft_plan_t* p = reinterpret_cast<ps_fft_plan_t*>(plan);
-  cudaStream_t st = S(stream);
+// power-of-two R2C / C2R on a core plan (also the engine under bluestein.cu)
+namespace ps {
+int fft_r2c_core(const ps_fft_plan_t* p, const float* d_in, float2* d_out, cudaStream_t st) {
   LoadPackedReal ld{reinterpret_cast<const float2*>(d_in), 0, 0, 0, nullptr};
   int rc = launch_pass1<false>(p, ld, st);
   if (rc) return rc;
   StoreNatural sn{reinterpret_cast<float2*>(p->Z), 0, 0, 0, nullptr};
   rc = launch_pass2<false>(p, sn, st);
   if (rc) return rc;
-  return launch_r2c_post(p, p->Z, reinterpret_cast<float2*>(d_out), st);
+  return launch_r2c_post(p, p->Z, d_out, st);
 }
 
-int ps_fft_c2r(ps_fft_plan* plan, const ps_complex* d_in, float* d_out, void* stream) {
-  if (!plan) return invalid("ps_fft_c2r: null plan");
-  const ps_fft_plan_t* p = reinterpret_cast<ps_fft_plan_t*>(plan);
-  cudaStream_t st = S(stream);
-  LoadC2RPre ld{reinterpret_cast<const float2*>(d_in), p->M, 0, 0};
+int fft_c2r_core(const ps_fft_plan_t* p, const float2* d_in, float* d_out, cudaStream_t st) {
+  LoadC2RPre ld{d_in, p->M, 0, 0};
   int rc = launch_pass1<true>(p, ld, st);
   if (rc) return rc;
   StoreNatural sn{reinterpret_cast<float2*>(d_out), 0, 0, 0, nullptr};
   return launch_pass2<true>(p, sn, st);
+}
+}  // namespace ps
+
+struct ps_fft_plan {
+  ps_fft_plan_t* core = nullptr;  // transform of length n, or of the chirp-z convolution length when blu is set
+  Bluestein* blu = nullptr;       // lengths that are not a power of two in [2^17, 2^25]
+};
+
+extern "C" {
+
+int ps_fft_plan_create(unsigned n, ps_fft_plan** out) {
+  if (!out) return invalid("ps_fft_plan_create: null output");
+  *out = nullptr;
+  const bool pow2 = n >= (1u << 17) && n <= (1u << 25) && !(n & (n - 1));
+  unsigned core_n = n;
+  if (!pow2) {
+    if (n < 2 || n > (1u << 24)) return invalid("ps_fft_plan_create: n must be in [2, 2^24], or a power of two up to 2^25");
+    core_n = bluestein_length(n);
+  }
+  ps_fft_plan* plan = new ps_fft_plan;
+  int rc = plan_create(core_n, &plan->core, 1);
+  if (!rc && !pow2) rc = bluestein_create(n, plan->core, &plan->blu);
+  if (rc) {
+    plan_destroy(plan->core);
+    delete plan;
+    return rc;
+  }
+  *out = plan;
+  return PS_OK;
+}
+
+void ps_fft_plan_destroy(ps_fft_plan* plan) {
+  if (!plan) return;
+  bluestein_destroy(plan->blu);
+  plan_destroy(plan->core);
+  delete plan;
+}
+
+int ps_fft_r2c(ps_fft_plan* plan, const float* d_in, ps_complex* d_out, void* stream) {
+  if (!plan) return invalid("ps_fft_r2c: null plan");
+  if (plan->blu) return bluestein_r2c(plan->blu, plan->core, d_in, reinterpret_cast<float2*>(d_out), S(stream));
+  return fft_r2c_core(plan->core, d_in, reinterpret_cast<float2*>(d_out), S(stream));
+}
+
+int ps_fft_c2r(ps_fft_plan* plan, const ps_complex* d_in, float* d_out, void* stream) {
+  if (!plan) return invalid("ps_fft_c2r: null plan");
+  if (plan->blu) return bluestein_c2r(plan->blu, plan->core, reinterpret_cast<const float2*>(d_in), d_out, S(stream));
+  return fft_c2r_core(plan->core, reinterpret_cast<const float2*>(d_in), d_out, S(stream));
 }
 
 }  // extern "C"

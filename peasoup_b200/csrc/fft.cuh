@@ -45,6 +45,16 @@ struct ps_fft_plan_t {
   FftTables tables() const { return FftTables{W4096, TA, TB}; }
 };
 
+// fft.cu: power-of-two transforms on a core plan; bluestein.cu: any length on top of them
+int fft_r2c_core(const ps_fft_plan_t* p, const float* d_in, float2* d_out, cudaStream_t st);
+int fft_c2r_core(const ps_fft_plan_t* p, const float2* d_in, float* d_out, cudaStream_t st);
+struct Bluestein;
+unsigned bluestein_length(unsigned n);
+int bluestein_create(unsigned n, const ps_fft_plan_t* core, Bluestein** out);
+void bluestein_destroy(Bluestein* b);
+int bluestein_r2c(const Bluestein* b, const ps_fft_plan_t* core, const float* d_in, float2* d_out, cudaStream_t st);
+int bluestein_c2r(const Bluestein* b, const ps_fft_plan_t* core, const float2* d_in, float* d_out, cudaStream_t st);
+
 // W_M^p for p < M from the two-level table (one complex multiply)
 __device__ __forceinline__ cf twiddle_M(const FftTables& t, unsigned p) {
   return psfft::cmul(psfft::ldg_cf(&t.TA[p >> 12]), psfft::ldg_cf(&t.TB[p & 4095u]));

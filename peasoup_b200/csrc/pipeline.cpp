@@ -5,6 +5,7 @@
 #include <thread>
 #include <chrono>
 #include "../../include/peasoup_b200/postprocess.hpp"
+#include "../../include/peasoup_b200/coincidencer.hpp"
 
 namespace ps {
 void set_error(const std::string& msg);
@@ -269,6 +270,28 @@ long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, 
       seconds4[0] = secs(t0, t1); seconds4[1] = secs(t1, t2); seconds4[2] = secs(t2, t3); seconds4[3] = secs(t0, t4);
     }
     return flatten(dm_cands, out, max_out);
+  } catch (std::exception& e) {
+    ps::set_error(e.what());
+    return PS_ECUDA;
+  }
+}
+
+// main() of src/coincidencer.cpp
+long ps_coincidence_files(const char* const* filenames, int nfiles, const ps_coincidence_params* p, float* h_samp_mask,
+                          size_t max_samp, float* h_spec_mask, size_t max_spec) {
+  try {
+    if (!filenames || nfiles < 1 || !p) ErrorChecker::throw_error("ps_coincidence_files: null argument");
+    std::vector<std::string> files(filenames, filenames + nfiles);
+    CoincidenceOptions args;
+    args.threshold = p->threshold;
+    args.beam_threshold = p->beam_threshold;
+    args.samp_outfilename = p->samp_outfilename ? p->samp_outfilename : "";
+    args.spec_outfilename = p->spec_outfilename ? p->spec_outfilename : "";
+    std::vector<float> samp, spec;
+    coincidence_match_files(files, args, &samp, &spec);
+    if (h_samp_mask) memcpy(h_samp_mask, samp.data(), sizeof(float) * std::min(max_samp, samp.size()));
+    if (h_spec_mask) memcpy(h_spec_mask, spec.data(), sizeof(float) * std::min(max_spec, spec.size()));
+    return (long)samp.size();
   } catch (std::exception& e) {
     ps::set_error(e.what());
     return PS_ECUDA;

@@ -41,3 +41,25 @@ def cand_keys(recs, nbins, bin_width_f, with_top=False):
             k = k + (int(r["is_top"]),)
         out[k] = float(r["snr"])
     return out
+
+
+def write_sigproc(path, data, tsamp, fch1, foff, nbits=8, source="synthetic"):
+    """Minimal SIGPROC filterbank writer (header.hpp:171-336 keys the reader needs).  data:
+    [nsamps][nchans] uint8 values already packed for nbits = 8."""
+    import struct
+
+    def s(x):
+        b = x.encode()
+        return struct.pack("<i", len(b)) + b
+
+    nsamps, nchans = data.shape
+    hdr = s("HEADER_START") + s("source_name") + s(source)
+    hdr += s("machine_id") + struct.pack("<i", 0) + s("telescope_id") + struct.pack("<i", 0)
+    hdr += s("data_type") + struct.pack("<i", 1)
+    hdr += s("fch1") + struct.pack("<d", fch1) + s("foff") + struct.pack("<d", foff)
+    hdr += s("nchans") + struct.pack("<i", nchans) + s("nbits") + struct.pack("<i", nbits)
+    hdr += s("tstart") + struct.pack("<d", 56000.0) + s("tsamp") + struct.pack("<d", tsamp)
+    hdr += s("nifs") + struct.pack("<i", 1) + s("HEADER_END")
+    with open(path, "wb") as f:
+        f.write(hdr)
+        f.write(np.ascontiguousarray(data, np.uint8).tobytes())

@@ -124,7 +124,38 @@ def test_large_size_properties(lib, lg):
 
 
 def test_plan_rejects_unsupported_sizes(lib):
-    for n in (0, 1000, 1 << 16, (1 << 17) + 2, 1 << 26):
+    for n in (0, 1, (1 << 24) + 1, 1 << 26):
         h = C.c_void_p()
         assert lib.ps_fft_plan_create(n, C.byref(h)) == -2
         assert b"power of two" in lib.ps_last_error()
+
+
+@pytest.mark.parametrize("n", [1000, 1 << 16, 99991, (1 << 17) + 2, 187520, 3 << 16, 1000001])
+def test_arbitrary_length_vs_numpy(lib, n):
+    """Lengths cuFFT would take but the power-of-two engine does not (the coincidencer transforms
+    the whole observation, coincidencer.cpp:137-139): chirp-z on top of the 2^k transforms."""
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(n) * 16).astype(np.float32)
+    plan = pb.FFTPlan(n)
+    dX = torch.zeros(2 * (n // 2 + 1), dtype=torch.float32, device="cuda")
+    plan.r2c(torch.from_numpy(x).cuda(), dX)
+    X = dX.cpu().numpy().view(np.complex64)
+    want = np.fft.rfft(x.astype(np.float64))
+    emax, erms = relerr(X, want)
+    assert emax < 5e-5 and erms < 5e-6, (emax, erms)
+    # u8-like input (large DC): the chirp spreads the DC term over the whole convolution
+    xo = (x + 128).astype(np.float32)
+    plan.r2c(torch.from_numpy(xo).cuda(), dX)
+    Xo = dX.cpu().numpy().view(np.complex64)
+    wo = np.fft.rfft(xo.astype(np.float64))
+    nrms = np.sqrt((np.abs(wo[1:]) ** 2).mean())
+    assert np.sqrt((np.abs(Xo[1:] - wo[1:]) ** 2).mean()) / nrms < 1e-4
+    assert abs(Xo[0] - wo[0]) / abs(wo[0]) < 1e-5
+    # C2R, unnormalised
+    Xc = want.astype(np.complex64)
+    dy = torch.zeros(n, dtype=torch.float32, device="cuda")
+    plan.c2r(torch.from_numpy(Xc.view(np.float32).copy()).cuda(), dy)
+    want_y = np.fft.irfft(Xc.astype(np.complex128), n) * n
+    emax, erms = relerr(dy.cpu().numpy(), want_y)
+    assert emax < 5e-5 and erms < 5e-6, (emax, erms)
+    plan.close()
