@@ -52,6 +52,19 @@ __device__ __forceinline__ float sqrt_approx(float x) {
   return r;
 }
 
+// normalised interbinned amplitude of one bin given its left neighbour (kernels.cu:231-252, :469-480)
+__device__ __forceinline__ float interbin_norm(float2 x, float2 left, float mean, float inv_sigma) {
+  const float ampsq = x.x * x.x + x.y * x.y;
+  const float dr = x.x - left.x, di = x.y - left.y;
+  const float diff = 0.5f * (dr * dr + di * di);
+  return (sqrt_approx(fmaxf(ampsq, diff)) - mean) * inv_sigma;
+}
+
+// One thread = bins [8g, 8g+8) AND their mirror images [M-8g-8, M-8g): the split of bin k and of
+// bin M-k share the same two packed values, E_{M-k} = conj E_k, O_{M-k} = conj O_k and
+// W_N^{M-k} = -conj W_N^k, so X_k = E + T and X_{M-k} = conj(E - T) with one T = W_N^k O.  Eleven
+// pairs k = 8g-1 .. 8g+9 give the 16 outputs and both left neighbours: 11 B of loads per bin
+// where the one-sided version read 20.  Thread 0 also writes the Nyquist bin M.
 __global__ void __launch_bounds__(256) spectrum_kernel(const float2* __restrict__ Zall, float* __restrict__ Pall, unsigned M,
                                                        size_t pstride, const float* __restrict__ stats, float fsize,
                                                        const cf* __restrict__ TC, const cf* __restrict__ TD, float2 w1) {
@@ -59,41 +72,52 @@ __global__ void __launch_bounds__(256) spectrum_kernel(const float2* __restrict_
   float* __restrict__ P = Pall + (size_t)blockIdx.y * pstride;
   const float mean = __fmul_rn(stats[0], fsize);
   const float inv_sigma = __fdiv_rn(1.0f, __fmul_rn(stats[2], fsize));
-  const unsigned ngroups = M / 4;  // bins [0, M) in groups of 4; bin M handled with the last group
+  const unsigned ngroups = M / 16;
   for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
-    const unsigned k0 = 4 * g;
-    const float4 za = *reinterpret_cast<const float4*>(&Z[k0]);           // Z[k0], Z[k0+1]
-    const float4 zb = *reinterpret_cast<const float4*>(&Z[k0 + 2]);       // Z[k0+2], Z[k0+3]
-    const float4 m12 = *reinterpret_cast<const float4*>(&Z[M - k0 - 2]);  // Z[M-k0-2], Z[M-k0-1]
-    const float2 m3 = Z[M - k0 - 3];
-    const float2 m0 = Z[k0 == 0 ? 0 : M - k0];  // Z[M] == Z[0]
-    const float2 zk[4] = {make_float2(za.x, za.y), make_float2(za.z, za.w), make_float2(zb.x, zb.y), make_float2(zb.z, zb.w)};
-    const float2 zm[4] = {m0, make_float2(m12.z, m12.w), make_float2(m12.x, m12.y), m3};
-    float2 w = twiddle_N(TC, TD, k0);
-    float2 left = make_float2(0.f, 0.f);  // left neighbour of bin 0 is zero (kernels.cu:236-241)
-    if (k0) {
-      // W_N^(k0-1) = W_N^k0 * conj(W_N^1)
-      float2 wl = make_float2(w.x * w1.x + w.y * w1.y, w.y * w1.x - w.x * w1.y);
-      left = split_bin(Z[k0 - 1], Z[M - k0 + 1], wl);
-    }
-    float out[4];
+    const unsigned k0 = 8 * g;
+    // zk[t] = Z[k0-1+t], zm[t] = Z[M-(k0-1+t)], t = 0..10
+    float2 zk[11], zm[11];
+    zk[0] = k0 ? Z[k0 - 1] : make_float2(0.f, 0.f);
+    zm[0] = k0 ? Z[M - k0 + 1] : make_float2(0.f, 0.f);
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const float2 x = split_bin(zk[j], zm[j], w);
-      const float ampsq = x.x * x.x + x.y * x.y;
-      const float dr = x.x - left.x, di = x.y - left.y;
-      const float diff = 0.5f * (dr * dr + di * di);
-      out[j] = (sqrt_approx(fmaxf(ampsq, diff)) - mean) * inv_sigma;
-      left = x;
+    for (int q = 0; q < 5; q++) {
+      const float4 a = *reinterpret_cast<const float4*>(&Z[k0 + 2 * q]);
+      zk[1 + 2 * q] = make_float2(a.x, a.y);
+      zk[2 + 2 * q] = make_float2(a.z, a.w);
+    }
+#pragma unroll
+    for (int q = 1; q < 5; q++) {  // Z[M-k0-2q], Z[M-k0-2q+1]
+      const float4 a = *reinterpret_cast<const float4*>(&Z[M - k0 - 2 * q]);
+      zm[1 + 2 * q] = make_float2(a.x, a.y);
+      zm[2 * q] = make_float2(a.z, a.w);
+    }
+    zm[1] = Z[k0 ? M - k0 : 0];  // Z[M] == Z[0]
+    zm[10] = Z[M - k0 - 9];
+    float2 w = twiddle_N(TC, TD, k0);
+    w = make_float2(w.x * w1.x + w.y * w1.y, w.y * w1.x - w.x * w1.y);  // W_N^(k0-1)
+    float2 xa_prev = make_float2(0.f, 0.f), xb_prev = make_float2(0.f, 0.f);
+    float outA[8], outB[8];
+#pragma unroll
+    for (int t = 0; t < 11; t++) {
+      const float2 zkk = zk[t], zmm = zm[t];
+      const float er = 0.5f * (zkk.x + zmm.x), ei = 0.5f * (zkk.y - zmm.y);
+      const float orr = 0.5f * (zkk.y + zmm.y), oi = -0.5f * (zkk.x - zmm.x);
+      const float tr = w.x * orr - w.y * oi, ti = w.x * oi + w.y * orr;
+      float2 xa = make_float2(er + tr, ei + ti);      // X[k0-1+t]
+      const float2 xb = make_float2(er - tr, ti - ei);  // X[M-(k0-1+t)] = conj(E - T)
+      if (t == 0 && k0 == 0) xa = make_float2(0.f, 0.f);  // left neighbour of bin 0 is zero
+      if (t >= 1 && t <= 8) outA[t - 1] = interbin_norm(xa, xa_prev, mean, inv_sigma);
+      // value X[M-(k0-1+(t-1))] with left neighbour X[M-(k0-1+t)]
+      if (t >= 3) outB[10 - t] = interbin_norm(xb_prev, xb, mean, inv_sigma);
+      if (t == 2 && k0 == 0) P[M] = interbin_norm(xb_prev, xb, mean, inv_sigma);  // Nyquist bin from the pair k = 0
+      xa_prev = xa;
+      xb_prev = xb;
       w = make_float2(w.x * w1.x - w.y * w1.y, w.x * w1.y + w.y * w1.x);
     }
-    *reinterpret_cast<float4*>(&P[k0]) = make_float4(out[0], out[1], out[2], out[3]);
-    if (k0 + 4 == M) {  // Nyquist bin: X[M] = Re Z0 - Im Z0
-      const float2 z0 = Z[0];
-      const float xr = z0.x - z0.y;
-      const float dr = xr - left.x, di = -left.y;
-      P[M] = (sqrt_approx(fmaxf(xr * xr, 0.5f * (dr * dr + di * di))) - mean) * inv_sigma;
-    }
+    *reinterpret_cast<float4*>(&P[k0]) = make_float4(outA[0], outA[1], outA[2], outA[3]);
+    *reinterpret_cast<float4*>(&P[k0 + 4]) = make_float4(outA[4], outA[5], outA[6], outA[7]);
+    *reinterpret_cast<float4*>(&P[M - k0 - 8]) = make_float4(outB[0], outB[1], outB[2], outB[3]);
+    *reinterpret_cast<float4*>(&P[M - k0 - 4]) = make_float4(outB[4], outB[5], outB[6], outB[7]);
   }
 }
 
@@ -471,6 +495,9 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   // TMA tensor-map tile stores (fft_pass*_tma_kernel) measured ~3 % slower than plain stores on
   // this workload (the passes are issue-bound, not store-latency-bound): opt-in via PS_TMA=1
   static const bool env_tma = getenv("PS_TMA") ? atoi(getenv("PS_TMA")) != 0 : false;
+  // profiling aid (tools/time_chain.py): leave kernels out of the chain to time the others;
+  // 1 = pass 1, 2 = pass 2, 4 = spectrum, 8 = harmonic sums + peaks.  Results are garbage when set.
+  static const int env_skip = getenv("PS_SKIP") ? atoi(getenv("PS_SKIP")) : 0;
   for (int j = 0; j < n_acc; j += env_batch) {
     const int nb = std::min(env_batch, n_acc - j);
     LoadResampled ld;
@@ -492,12 +519,12 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
       if ((rc = launch_pass1_tma<false>(p, ld, st, nb))) return rc;
       if ((rc = launch_pass2_tma<false>(p, st, nb))) return rc;
     } else {
-      if ((rc = launch_pass1<false>(p, ld, st, nb))) return rc;
+      if (!(env_skip & 1) && (rc = launch_pass1<false>(p, ld, st, nb))) return rc;
       StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
-      if ((rc = launch_pass2<false>(p, sn, st, nb))) return rc;
+      if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb))) return rc;
     }
-    if (!s->fused) {
-      dim3 g1(ew_grid(p->M / 4, 256, 1), nb);
+    if (!s->fused && !(env_skip & 4)) {
+      dim3 g1(ew_grid(p->M / 16, 256, 1), nb);
       spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
                                           (float)size, p->TC, p->TD,
                                           make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
@@ -507,6 +534,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
 #define PS_HP(NF)                                                                                                \
   harmonic_peaks_kernel<NF><<<g2, 128, 0, st>>>(s->d_pbatch, (int)s->nbins, s->pstride, s->ranges, s->scales,   \
                                                  s->prm.min_snr, acc_idx0 + j, sink)
+    if (env_skip & 8) continue;
     switch (s->prm.nharmonics) {
       case 0: PS_HP(0); break;
       case 1: PS_HP(1); break;
