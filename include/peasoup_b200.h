@@ -165,6 +165,13 @@ int ps_search_accel_batch(ps_search* s, const float* h_acc, int n_acc, int acc_i
  * (acc_idx, nh, bin), i.e. the order the reference's per-spectrum copy_if calls produce). */
 int ps_search_reset_peaks(ps_search* s, void* stream);
 long ps_search_fetch_peaks(ps_search* s, ps_raw_peak* h_out, size_t max_out, void* stream);
+/* The harmonic-sum + threshold + compaction stage on its own (HarmonicFolder::fold +
+ * PeakFinder::find_candidates, harmonicfolder.hpp:26-38 + peakfinder.hpp:72-94, without
+ * materialising the sums): nbatch normalised spectra of size/2+1 bins, `stride` floats apart,
+ * spectrum b reported as acceleration index acc_idx0 + b.  Peaks join the handle's peak list
+ * (ps_search_reset_peaks / ps_search_fetch_peaks).  Also BASELINE.json configs[2]'s microbench. */
+int ps_search_harmonic_peaks(ps_search* s, const float* d_spectra, size_t stride, int nbatch,
+                             int acc_idx0, void* stream);
 /* Diagnostics for stage-by-stage parity tests: device pointers owned by the handle. */
 const float* ps_search_whitened_series(ps_search* s);   /* size floats */
 const float* ps_search_last_spectrum(ps_search* s);     /* size/2+1 floats (last accel trial) */

@@ -352,7 +352,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // thread 0 fetches the NEXT tile with a single bulk copy into a staging buffer while the current
 // tile is transformed (issued once every thread has taken its operands out of the staging buffer).
 template <int R3, bool INV, class Storer>
-__global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer st, FftTables t, int n1, int n2, int nbatch) {
+__global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer st, FftTables t, int n1, int n2, int nbatch, int reverse) {
   using C = psfft::CtaFft<R3, INV>;
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) unsigned long long bar;
@@ -361,17 +361,20 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
   const size_t tile_elems = (size_t)n2 * C::F;  // complex words per tile, contiguous in Yt
   constexpr unsigned kTileBytes = sizeof(cf) * 16 * C::THREADS;
   cf* stage = reinterpret_cast<cf*>(smem + C::SMEM_WORDS);
-  int work = blockIdx.x;
-  if (work >= nwork) return;
+  // reverse = 1 walks the work items backwards: pass 1 wrote the LAST batch item most recently, so
+  // starting there finds its inter-pass data still in L2 (the batch does not fit as a whole)
+  int slot = blockIdx.x;
+  if (slot >= nwork) return;
   if (threadIdx.x == 0) {
     mbar_init(&bar, 1);
     fence_proxy_async();
     mbar_expect_tx(&bar, kTileBytes);
-    bulk_g2s(stage, Yt + (size_t)work * tile_elems, kTileBytes, &bar);
+    bulk_g2s(stage, Yt + (size_t)(reverse ? nwork - 1 - slot : slot) * tile_elems, kTileBytes, &bar);
   }
   __syncthreads();
   unsigned parity = 0;
-  for (; work < nwork; work += gridDim.x) {
+  for (; slot < nwork; slot += gridDim.x) {
+    const int work = reverse ? nwork - 1 - slot : slot;
     const int b = work / ntiles, tile = work - b * ntiles;
     st.begin(b, tile * C::F, n1);
     mbar_wait(&bar, parity);
@@ -381,8 +384,9 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
     for (int a = 0; a < 16; a++) v[a] = stage[a * C::THREADS + threadIdx.x];
     C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
     __syncthreads();  // E1 complete; every thread has taken its operands out of the staging buffer
-    const int next = work + gridDim.x;
-    if (threadIdx.x == 0 && next < nwork) {
+    const int next_slot = slot + gridDim.x;
+    if (threadIdx.x == 0 && next_slot < nwork) {
+      const int next = reverse ? nwork - 1 - next_slot : next_slot;
       fence_proxy_async();
       mbar_expect_tx(&bar, kTileBytes);
       bulk_g2s(stage, Yt + (size_t)next * tile_elems, kTileBytes, &bar);
@@ -559,14 +563,14 @@ inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t
 }
 
 template <int R3, bool INV, class Storer>
-inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch) {
+inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch, int reverse) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass2_kernel<R3, INV, Storer>;
   static bool done[64] = {};
   const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;  // exchange buffers + TMA staging tile
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
-  k<<<fft_grid(p->n1 / C::F * nbatch), C::THREADS, smem, st>>>(p->Yt, stor, p->tables(), p->n1, p->n2, nbatch);
+  k<<<fft_grid(p->n1 / C::F * nbatch), C::THREADS, smem, st>>>(p->Yt, stor, p->tables(), p->n1, p->n2, nbatch, reverse);
   PS_LAUNCHED("fft_pass2_kernel");
   return PS_OK;
 }
@@ -589,8 +593,8 @@ inline int launch_pass1(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t s
 }
 
 template <bool INV, class Storer>
-inline int launch_pass2(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch = 1) {
-#define PS_CALL2(R) launch_pass2_r<R, INV, Storer>(p, stor, st, nbatch)
+inline int launch_pass2(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch = 1, int reverse = 0) {
+#define PS_CALL2(R) launch_pass2_r<R, INV, Storer>(p, stor, st, nbatch, reverse)
   PS_DISPATCH_R(p->r2, PS_CALL2)
 #undef PS_CALL2
 }

@@ -483,6 +483,38 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   return PS_OK;
 }
 
+// harmonic sums + peaks of nb spectra (blockIdx.y = spectrum)
+static int launch_harmonic_peaks(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
+  PeakSink sink{s->d_peaks, s->d_count, s->cap};
+  dim3 g2((((unsigned)s->nbins + 511) / 512 + 3) / 4, nb);
+#define PS_HP(NF)                                                                                                          \
+  harmonic_peaks_kernel<NF><<<g2, 128, 0, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, \
+                                                 acc_idx0, sink)
+  switch (s->prm.nharmonics) {
+    case 0: PS_HP(0); break;
+    case 1: PS_HP(1); break;
+    case 2: PS_HP(2); break;
+    case 3: PS_HP(3); break;
+    case 4: PS_HP(4); break;
+    default: PS_HP(5); break;
+  }
+#undef PS_HP
+  PS_LAUNCHED("harmonic_peaks_kernel");
+  return PS_OK;
+}
+
+int ps_search_harmonic_peaks(ps_search* hs, const float* d_spectra, size_t stride, int nbatch, int acc_idx0, void* stream) {
+  Search* s = SS(hs);
+  if (!s || !d_spectra) return invalid("ps_search_harmonic_peaks: null argument");
+  if (nbatch < 0 || stride < s->nbins) return invalid("ps_search_harmonic_peaks: stride must be >= size/2+1");
+  for (int j = 0; j < nbatch; j += 32768) {  // grid.y limit
+    int nb = std::min(32768, nbatch - j);
+    int rc = launch_harmonic_peaks(s, d_spectra + (size_t)j * stride, stride, nb, acc_idx0 + j, S(stream));
+    if (rc) return rc;
+  }
+  return PS_OK;
+}
+
 int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_idx0, void* stream) {
   Search* s = SS(hs);
   if (!s) return invalid("ps_search_accel_batch: null handle");
@@ -490,7 +522,6 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   const ps_fft_plan_t* p = s->plan;
   unsigned size = s->prm.size;
   int rc;
-  PeakSink sink{s->d_peaks, s->d_count, s->cap};
   static const int env_batch = getenv("PS_BATCH") ? std::max(1, std::min(kAccelBatch, atoi(getenv("PS_BATCH")))) : kAccelBatch;
   // TMA tensor-map tile stores (fft_pass*_tma_kernel) measured ~3 % slower than plain stores on
   // this workload (the passes are issue-bound, not store-latency-bound): opt-in via PS_TMA=1
@@ -498,6 +529,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   // profiling aid (tools/time_chain.py): leave kernels out of the chain to time the others;
   // 1 = pass 1, 2 = pass 2, 4 = spectrum, 8 = harmonic sums + peaks.  Results are garbage when set.
   static const int env_skip = getenv("PS_SKIP") ? atoi(getenv("PS_SKIP")) : 0;
+  static const int env_rev = getenv("PS_REVERSE") ? atoi(getenv("PS_REVERSE")) : 1;
   for (int j = 0; j < n_acc; j += env_batch) {
     const int nb = std::min(env_batch, n_acc - j);
     LoadResampled ld;
@@ -521,7 +553,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     } else {
       if (!(env_skip & 1) && (rc = launch_pass1<false>(p, ld, st, nb))) return rc;
       StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
-      if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb))) return rc;
+      if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb, env_rev))) return rc;
     }
     if (!s->fused && !(env_skip & 4)) {
       dim3 g1(ew_grid(p->M / 16, 256, 1), nb);
@@ -530,21 +562,8 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
                                           make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
       PS_LAUNCHED("spectrum_kernel");
     }
-    dim3 g2((((unsigned)s->nbins + 511) / 512 + 3) / 4, nb);
-#define PS_HP(NF)                                                                                                \
-  harmonic_peaks_kernel<NF><<<g2, 128, 0, st>>>(s->d_pbatch, (int)s->nbins, s->pstride, s->ranges, s->scales,   \
-                                                 s->prm.min_snr, acc_idx0 + j, sink)
     if (env_skip & 8) continue;
-    switch (s->prm.nharmonics) {
-      case 0: PS_HP(0); break;
-      case 1: PS_HP(1); break;
-      case 2: PS_HP(2); break;
-      case 3: PS_HP(3); break;
-      case 4: PS_HP(4); break;
-      default: PS_HP(5); break;
-    }
-#undef PS_HP
-    PS_LAUNCHED("harmonic_peaks_kernel");
+    if ((rc = launch_harmonic_peaks(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st))) return rc;
   }
   s->last_spectrum = s->d_pbatch + (size_t)((n_acc - 1) % env_batch) * s->pstride;
   return PS_OK;

@@ -79,6 +79,10 @@ class Search:
         a = np.ascontiguousarray(accs, np.float32)
         check(load().ps_search_accel_batch(self._h, ptr(a), len(a), acc_idx0, stream_ptr(stream)))
 
+    def harmonic_peaks(self, d_spectra, stride, nbatch, acc_idx0=0, stream=None):
+        """Harmonic sums + peaks of `nbatch` normalised spectra already on the device."""
+        check(load().ps_search_harmonic_peaks(self._h, ptr(d_spectra), stride, nbatch, acc_idx0, stream_ptr(stream)))
+
     def reset_peaks(self, stream=None):
         check(load().ps_search_reset_peaks(self._h, stream_ptr(stream)))
 

@@ -272,3 +272,35 @@ def test_full_size_injected_pulsar_properties(lib, oracle):
     assert not np.any((np.abs(got["freq"] - 50.0) < 0.05) | (np.abs(got["freq"] - 100.0) < 0.05))
     # the acceleration distiller keeps the neighbouring-acceleration detections as associates
     assert (got["is_top"] == 0).sum() > 0
+
+
+@pytest.mark.parametrize("size,nbatch", [(1 << 17, 3), (1 << 20, 2)])
+def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch):
+    """ps_search_harmonic_peaks on spectra supplied by the caller (BASELINE.json configs[2]'s stage):
+    same bins, same levels and bit-identical S/N as harmonic_sum_kernel + device_find_peaks."""
+    tsamp, thresh = 64e-6, 5.0
+    cfg = oracle.SearchConfig(size, tsamp, min_snr=thresh)
+    rng = np.random.default_rng(size + nbatch)
+    stride = cfg.nbins + 7  # spectra need not be packed
+    spectra = np.zeros((nbatch, stride), np.float32)
+    for b in range(nbatch):
+        p = rng.normal(0, 1, cfg.nbins).astype(np.float32)
+        p[::32] += 1.0                                        # harmonic_sum_test.cpp's pattern
+        f0 = 1000 + 37 * b
+        p[f0 * np.arange(1, 17)] += 6.0                       # comb: fundamental + 15 harmonics
+        spectra[b, :cfg.nbins] = p
+    s = pb.Search(make_search_params(size, size, tsamp, min_snr=thresh))
+    s.reset_peaks()
+    d = torch.from_numpy(spectra).cuda()
+    s.harmonic_peaks(d, stride, nbatch, acc_idx0=10)
+    peaks = s.fetch_peaks()
+    want = {}
+    for b in range(nbatch):
+        for nh, (idx, snr, _) in enumerate(oracle.spectrum_raw_peaks(spectra[b, :cfg.nbins], cfg)):
+            for i, v in zip(idx, snr):
+                want[(10 + b, nh, int(i))] = np.float32(v)
+    got = {(int(r["acc_idx"]), int(r["nh"]), int(r["bin"])): np.float32(r["snr"]) for r in peaks}
+    assert len(want) > 50 and set(got) == set(want)
+    assert all(got[k] == want[k] for k in want)
+    assert any(k[1] == 4 and k[2] == 1000 * 16 for k in got)  # the comb is found at the top level
+    s.close()
