@@ -304,3 +304,22 @@ def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch):
     assert all(got[k] == want[k] for k in want)
     assert any(k[1] == 4 and k[2] == 1000 * 16 for k in got)  # the comb is found at the top level
     s.close()
+
+
+@pytest.mark.parametrize("size,acc_hi,a_inj", [(1 << 23, 50.0, 31.4), (1 << 24, 500.0, 312.5)])
+def test_survey_sizes_vs_reference_cuda_build(lib, oracle, ref, size, acc_hi, a_inj):
+    """BASELINE.json configs[3] and [4] shapes (2^23 samples, +-50 m/s^2; 2^24 samples, +-500 m/s^2)
+    on one DM trial and a handful of accelerations: identical candidates to the unmodified
+    reference build.  At 2^24 samples the loader's float32 index shortcut is out of range for half
+    the series and the reference's FP64 expression decides every index."""
+    tsamp = 64e-6
+    nsamps = size + 4096
+    trials = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=a_inj, amp=3.0, seed=size % 1000)
+    accs = np.array([0.0, -acc_hi, -acc_hi / 2, a_inj, acc_hi], np.float32)
+    dms = np.array([12.5], np.float32)
+    cfg = oracle.SearchConfig(size, tsamp)
+    want, _ = ref_search(ref, trials, dms, accs, size, nsamps, tsamp)
+    got, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs)
+    assert done == len(accs) and len(want) > 5
+    compare_candidates(got, want, cfg)
+    assert np.any((got["acc"] == np.float32(a_inj)) & (got["snr"] > 20))  # the injected pulsar, at its acceleration
