@@ -310,8 +310,8 @@ def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch):
 def test_survey_sizes_vs_reference_cuda_build(lib, oracle, ref, size, acc_hi, a_inj):
     """BASELINE.json configs[3] and [4] shapes (2^23 samples, +-50 m/s^2; 2^24 samples, +-500 m/s^2)
     on one DM trial and a handful of accelerations: identical candidates to the unmodified
-    reference build.  At 2^24 samples the loader's float32 index shortcut is out of range for half
-    the series and the reference's FP64 expression decides every index."""
+    reference build.  At 2^24 samples and 500 m/s^2 the resampling shift reaches ~3700 samples and
+    crosses a rounding boundary far more often than in the other tests (FP64 fallback of the loader)."""
     tsamp = 64e-6
     nsamps = size + 4096
     trials = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=a_inj, amp=3.0, seed=size % 1000)
