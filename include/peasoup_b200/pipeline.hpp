@@ -72,9 +72,11 @@ class WorkerSlots {
 
   WorkerSlots(int device, const ps_search_params& prm, const std::vector<float>& zf, const std::vector<float>& zw)
       : device(device), prm(prm), ncopy(std::min(prm.nsamps, prm.size)) {
-    // DM trials in flight per worker: their kernels interleave on the device (different streams)
-    // and hide each other's latency; PS_SLOTS overrides the default of 4
-    nslots = 4;
+    // DM trials in flight per worker: the next trial's copy, whitening and kernels are queued while
+    // the host distills the previous one.  With 32 acceleration trials per launch two are enough
+    // (measured trials/s at 1/2/3/4: 11.7k / 16.1k / 15.8k / 15.6k -- more slots only compete for
+    // the L2); PS_SLOTS overrides.
+    nslots = 2;
     if (const char* e = getenv("PS_SLOTS")) nslots = std::max(1, std::min((int)kMaxSlots, atoi(e)));
     ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
     const unsigned cap = prm.max_peaks ? prm.max_peaks : (1u << 20);

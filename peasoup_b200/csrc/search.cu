@@ -19,7 +19,7 @@
 namespace ps {
 
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
-constexpr int kAccelBatch = 4;  // acceleration trials per launch (fills the tail of the 148-SM waves; measured 1: 94, 2: 74, 4: 68 us/trial)
+constexpr int kAccelBatch = 32;  // acceleration trials per launch: amortises kernel ramp-up/drain and the 148-SM wave tail (measured us/trial: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7)
 void plan_destroy(ps_fft_plan_t* p);
 
 struct LevelRanges {
@@ -530,8 +530,12 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   // 1 = pass 1, 2 = pass 2, 4 = spectrum, 8 = harmonic sums + peaks.  Results are garbage when set.
   static const int env_skip = getenv("PS_SKIP") ? atoi(getenv("PS_SKIP")) : 0;
   static const int env_rev = getenv("PS_REVERSE") ? atoi(getenv("PS_REVERSE")) : 1;
-  for (int j = 0; j < n_acc; j += env_batch) {
-    const int nb = std::min(env_batch, n_acc - j);
+  // balanced launches: 101 trials at up to 16 per launch run as 15+15+15+14+14+14+14, not 6x16+5
+  int launches_left = (n_acc + env_batch - 1) / env_batch;
+  int last_nb = 1;
+  for (int j = 0, nb = 0; j < n_acc; j += nb, launches_left--) {
+    nb = (n_acc - j + launches_left - 1) / launches_left;
+    last_nb = nb;
     LoadResampled ld;
     ld.D = reinterpret_cast<const float2*>(s->d_tim);
     ld.n1 = s->col_len;
@@ -565,7 +569,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     if (env_skip & 8) continue;
     if ((rc = launch_harmonic_peaks(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st))) return rc;
   }
-  s->last_spectrum = s->d_pbatch + (size_t)((n_acc - 1) % env_batch) * s->pstride;
+  s->last_spectrum = s->d_pbatch + (size_t)(last_nb - 1) * s->pstride;
   return PS_OK;
 }
 

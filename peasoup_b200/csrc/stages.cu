@@ -169,13 +169,28 @@ __global__ void __launch_bounds__(256) sums_kernel(const float* __restrict__ d, 
 }
 
 // stats.hpp:20-33 + kernels.cu:426-454 in float, no contraction: out = {mean, rms, std}
-__global__ void finalize_stats_kernel(const double* __restrict__ partials, int nparts, float count, float* __restrict__ out) {
-  if (threadIdx.x || blockIdx.x) return;
+__global__ void __launch_bounds__(256) finalize_stats_kernel(const double* __restrict__ partials, int nparts, float count,
+                                                             float* __restrict__ out) {
+  // one CTA: strided partial sums, then a fixed-order tree (deterministic; double accumulators)
+  __shared__ double sh[2][256];
   double s = 0, q = 0;
-  for (int i = 0; i < nparts; i++) {
+  for (int i = threadIdx.x; i < nparts; i += 256) {
     s += partials[2 * i];
     q += partials[2 * i + 1];
   }
+  sh[0][threadIdx.x] = s;
+  sh[1][threadIdx.x] = q;
+  __syncthreads();
+  for (int o = 128; o; o >>= 1) {
+    if ((int)threadIdx.x < o) {
+      sh[0][threadIdx.x] += sh[0][threadIdx.x + o];
+      sh[1][threadIdx.x] += sh[1][threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x) return;
+  s = sh[0][0];
+  q = sh[1][0];
   float rms = sqrtf(__fdiv_rn((float)q, count));
   float mean = __fdiv_rn((float)s, count);
   float sd = sqrtf(__fsub_rn(__fmul_rn(rms, rms), __fmul_rn(mean, mean)));
@@ -206,7 +221,7 @@ int launch_stats(const float* d, size_t n, double* d_partials, float* d_out3, cu
   int np = 0;
   int rc = launch_sums(d, n, d_partials, &np, st);
   if (rc) return rc;
-  finalize_stats_kernel<<<1, 32, 0, st>>>(d_partials, np, (float)(int)n, d_out3);
+  finalize_stats_kernel<<<1, 256, 0, st>>>(d_partials, np, (float)(int)n, d_out3);
   PS_LAUNCHED("finalize_stats_kernel");
   return PS_OK;
 }
