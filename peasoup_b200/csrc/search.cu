@@ -19,6 +19,8 @@
 namespace ps {
 
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
+constexpr int kP2sGrid = 148;           // CTAs of the fused pass-2 + spectrum kernel (one per SM)
+constexpr int kP2sLag = 2 * kP2sGrid;   // positions between a tile and the spectrum item that reads it
 constexpr int kAccelBatch = 32;  // acceleration trials per launch: amortises kernel ramp-up/drain and the 148-SM wave tail (measured us/trial: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7)
 void plan_destroy(ps_fft_plan_t* p);
 
@@ -60,6 +62,36 @@ __device__ __forceinline__ float interbin_norm(float2 x, float2 left, float mean
   return (sqrt_approx(fmaxf(ampsq, diff)) - mean) * inv_sigma;
 }
 
+// The eleven pairs of one thread (see spectrum_kernel): zk[t] = Z[k0-1+t], zm[t] = Z[M-(k0-1+t)];
+// wk0 = W_N^k0, w1 = W_N^1.  Writes bins [k0, k0+8), [M-k0-8, M-k0) and, for k0 = 0, bin M.
+__device__ __forceinline__ void spectrum_pairs(const float2* zk, const float2* zm, float2 wk0, float2 w1, unsigned k0, unsigned M,
+                                               float mean, float inv_sigma, float* __restrict__ P) {
+  float2 w = make_float2(wk0.x * w1.x + wk0.y * w1.y, wk0.y * w1.x - wk0.x * w1.y);  // W_N^(k0-1)
+  float2 xa_prev = make_float2(0.f, 0.f), xb_prev = make_float2(0.f, 0.f);
+  float outA[8], outB[8];
+#pragma unroll
+  for (int t = 0; t < 11; t++) {
+    const float2 zkk = zk[t], zmm = zm[t];
+    const float er = 0.5f * (zkk.x + zmm.x), ei = 0.5f * (zkk.y - zmm.y);
+    const float orr = 0.5f * (zkk.y + zmm.y), oi = -0.5f * (zkk.x - zmm.x);
+    const float tr = w.x * orr - w.y * oi, ti = w.x * oi + w.y * orr;
+    float2 xa = make_float2(er + tr, ei + ti);      // X[k0-1+t]
+    const float2 xb = make_float2(er - tr, ti - ei);  // X[M-(k0-1+t)] = conj(E - T)
+    if (t == 0 && k0 == 0) xa = make_float2(0.f, 0.f);  // left neighbour of bin 0 is zero
+    if (t >= 1 && t <= 8) outA[t - 1] = interbin_norm(xa, xa_prev, mean, inv_sigma);
+    // value X[M-(k0-1+(t-1))] with left neighbour X[M-(k0-1+t)]
+    if (t >= 3) outB[10 - t] = interbin_norm(xb_prev, xb, mean, inv_sigma);
+    if (t == 2 && k0 == 0) P[M] = interbin_norm(xb_prev, xb, mean, inv_sigma);  // Nyquist bin from the pair k = 0
+    xa_prev = xa;
+    xb_prev = xb;
+    w = make_float2(w.x * w1.x - w.y * w1.y, w.x * w1.y + w.y * w1.x);
+  }
+  *reinterpret_cast<float4*>(&P[k0]) = make_float4(outA[0], outA[1], outA[2], outA[3]);
+  *reinterpret_cast<float4*>(&P[k0 + 4]) = make_float4(outA[4], outA[5], outA[6], outA[7]);
+  *reinterpret_cast<float4*>(&P[M - k0 - 8]) = make_float4(outB[0], outB[1], outB[2], outB[3]);
+  *reinterpret_cast<float4*>(&P[M - k0 - 4]) = make_float4(outB[4], outB[5], outB[6], outB[7]);
+}
+
 // One thread = bins [8g, 8g+8) AND their mirror images [M-8g-8, M-8g): the split of bin k and of
 // bin M-k share the same two packed values, E_{M-k} = conj E_k, O_{M-k} = conj O_k and
 // W_N^{M-k} = -conj W_N^k, so X_k = E + T and X_{M-k} = conj(E - T) with one T = W_N^k O.  Eleven
@@ -93,33 +125,13 @@ __global__ void __launch_bounds__(256) spectrum_kernel(const float2* __restrict_
     }
     zm[1] = Z[k0 ? M - k0 : 0];  // Z[M] == Z[0]
     zm[10] = Z[M - k0 - 9];
-    float2 w = twiddle_N(TC, TD, k0);
-    w = make_float2(w.x * w1.x + w.y * w1.y, w.y * w1.x - w.x * w1.y);  // W_N^(k0-1)
-    float2 xa_prev = make_float2(0.f, 0.f), xb_prev = make_float2(0.f, 0.f);
-    float outA[8], outB[8];
-#pragma unroll
-    for (int t = 0; t < 11; t++) {
-      const float2 zkk = zk[t], zmm = zm[t];
-      const float er = 0.5f * (zkk.x + zmm.x), ei = 0.5f * (zkk.y - zmm.y);
-      const float orr = 0.5f * (zkk.y + zmm.y), oi = -0.5f * (zkk.x - zmm.x);
-      const float tr = w.x * orr - w.y * oi, ti = w.x * oi + w.y * orr;
-      float2 xa = make_float2(er + tr, ei + ti);      // X[k0-1+t]
-      const float2 xb = make_float2(er - tr, ti - ei);  // X[M-(k0-1+t)] = conj(E - T)
-      if (t == 0 && k0 == 0) xa = make_float2(0.f, 0.f);  // left neighbour of bin 0 is zero
-      if (t >= 1 && t <= 8) outA[t - 1] = interbin_norm(xa, xa_prev, mean, inv_sigma);
-      // value X[M-(k0-1+(t-1))] with left neighbour X[M-(k0-1+t)]
-      if (t >= 3) outB[10 - t] = interbin_norm(xb_prev, xb, mean, inv_sigma);
-      if (t == 2 && k0 == 0) P[M] = interbin_norm(xb_prev, xb, mean, inv_sigma);  // Nyquist bin from the pair k = 0
-      xa_prev = xa;
-      xb_prev = xb;
-      w = make_float2(w.x * w1.x - w.y * w1.y, w.x * w1.y + w.y * w1.x);
-    }
-    *reinterpret_cast<float4*>(&P[k0]) = make_float4(outA[0], outA[1], outA[2], outA[3]);
-    *reinterpret_cast<float4*>(&P[k0 + 4]) = make_float4(outA[4], outA[5], outA[6], outA[7]);
-    *reinterpret_cast<float4*>(&P[M - k0 - 8]) = make_float4(outB[0], outB[1], outB[2], outB[3]);
-    *reinterpret_cast<float4*>(&P[M - k0 - 4]) = make_float4(outB[4], outB[5], outB[6], outB[7]);
+    spectrum_pairs(zk, zm, twiddle_N(TC, TD, k0), w1, k0, M, mean, inv_sigma, P);
   }
 }
+
+}  // namespace ps
+#include "pass2spec.cuh"
+namespace ps {
 
 struct PeakSink {
   ps_raw_peak* peaks;
@@ -317,6 +329,9 @@ struct Search {
   LevelRanges ranges;
   LevelScales scales;
   float* d_pbatch = nullptr;   // kBatch spectra (stride pstride floats)
+  float2* d_ring = nullptr;    // pass2spec.cuh: ring of pass-2 tiles (packed spectrum rows), L2-resident
+  int* d_progress = nullptr;   // pass2spec.cuh: per-CTA progress counters
+  int ring_slots = 0;          // 0: the fused pass-2 + spectrum kernel is not used for this size
   size_t pstride = 0;
   const float* last_spectrum = nullptr;
   float bin_width_f = 0.f;   // float bin_width = 1.0/tobs   (pipeline_multi.cu:118-119)
@@ -328,7 +343,7 @@ static void free_search(Search* s) {
   plan_destroy(s->plan);
   cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
-  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch); cudaFree(s->d_yr);
+  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch); cudaFree(s->d_ring); cudaFree(s->d_progress); cudaFree(s->d_yr);
   delete s;
 }
 
@@ -412,6 +427,15 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (e == cudaSuccess) e = cudaMalloc(&s->d_peaks, sizeof(ps_raw_peak) * (size_t)s->cap);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_count, sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * kAccelBatch);
+  // fused pass 2 + spectrum (pass2spec.cuh; 2048-point rows in 4-row tiles): parity-green, keeps the
+  // packed spectrum out of DRAM, but measured slower than the two kernels (31.5 vs 21.0 us/trial
+  // for this portion: one 512-thread CTA per SM exposes every L2 round trip of the spectrum part),
+  // so it is opt-in: PS_P2S=1
+  if (e == cudaSuccess && !s->fused && s->plan->r2 == 8 && s->plan->n1 >= 64 && getenv("PS_P2S") && atoi(getenv("PS_P2S")) == 1) {
+    s->ring_slots = 2 * kP2sLag + kP2sGrid + 28;  // >= 2 lag + grid + 16 (pass2spec.cuh)
+    e = cudaMalloc(&s->d_ring, sizeof(float2) * (size_t)s->ring_slots * 4 * s->plan->n2);
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_progress, sizeof(int) * kP2sGrid);
+  }
   if (e == cudaSuccess && s->fused) e = cudaMalloc(&s->d_yr, sizeof(cf) * s->geom.ystride * kAccelBatch);
   if (e == cudaSuccess) e = cudaMemset(s->d_count, 0, sizeof(unsigned));
   if (e != cudaSuccess) {
@@ -480,6 +504,34 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
     if (h_mean) *h_mean = h[0];
     if (h_std) *h_std = h[2];
   }
+  return PS_OK;
+}
+
+// Z -> normalised interbinned spectra of nb trials
+static int launch_spectrum(Search* s, int nb, cudaStream_t st) {
+  const ps_fft_plan_t* p = s->plan;
+  dim3 g1(ew_grid(p->M / 16, 256, 1), nb);
+  spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
+                                      (float)s->prm.size, p->TC, p->TD,
+                                      make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
+  PS_LAUNCHED("spectrum_kernel");
+  return PS_OK;
+}
+
+// pass 2 + spectrum in one persistent kernel (pass2spec.cuh)
+static int launch_pass2_spec(Search* s, int nb, cudaStream_t st) {
+  const ps_fft_plan_t* p = s->plan;
+  using C = psfft::CtaFft<8, false>;
+  auto k = fft_pass2_spec_kernel<8>;
+  static bool done[64] = {};
+  const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;
+  int rc = configure_smem(k, smem, p->device, done);
+  if (rc) return rc;
+  PS_CUDA(cudaMemsetAsync(s->d_progress, 0, sizeof(int) * kP2sGrid, st), "launch_pass2_spec");
+  SpecArgs sa{s->d_pbatch, s->pstride, s->d_stats, (float)s->prm.size, p->TC, p->TD,
+              make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M))};
+  k<<<kP2sGrid, C::THREADS, smem, st>>>(p->Yt, s->d_ring, s->ring_slots, s->d_progress, p->tables(), p->n1, p->n2, nb, kP2sLag, sa, getenv("PS_DBG") ? atoi(getenv("PS_DBG")) : 0);
+  PS_LAUNCHED("fft_pass2_spec_kernel");
   return PS_OK;
 }
 
@@ -554,17 +606,16 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     } else if (p->has_tma && env_tma) {
       if ((rc = launch_pass1_tma<false>(p, ld, st, nb))) return rc;
       if ((rc = launch_pass2_tma<false>(p, st, nb))) return rc;
+      if ((rc = launch_spectrum(s, nb, st))) return rc;
     } else {
       if (!(env_skip & 1) && (rc = launch_pass1<false>(p, ld, st, nb))) return rc;
-      StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
-      if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb, env_rev))) return rc;
-    }
-    if (!s->fused && !(env_skip & 4)) {
-      dim3 g1(ew_grid(p->M / 16, 256, 1), nb);
-      spectrum_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_pbatch, p->M, s->pstride, s->d_stats,
-                                          (float)size, p->TC, p->TD,
-                                          make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M)));
-      PS_LAUNCHED("spectrum_kernel");
+      if (s->ring_slots && !(env_skip & 6)) {
+        if ((rc = launch_pass2_spec(s, nb, st))) return rc;
+      } else {
+        StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
+        if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb, env_rev))) return rc;
+        if (!(env_skip & 4) && (rc = launch_spectrum(s, nb, st))) return rc;
+      }
     }
     if (env_skip & 8) continue;
     if ((rc = launch_harmonic_peaks(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st))) return rc;
