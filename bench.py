@@ -37,6 +37,11 @@ NSAMPS = SIZE + 4096
 TSAMP = 64e-6
 ACCS = np.arange(-50, 51, 1, dtype=np.float32)
 NFOLDS = 4
+# dram__bytes_read.sum + dram__bytes_write.sum of the four chain kernels, per acceleration trial, from the
+# committed ncu launch list of `tools/profile_chain.py 26` (26 trials per launch): pass 1 40.4 MB,
+# pass 2 65.1 MB, spectrum 49.0 MB, harmonic sums + peaks 16.8 MB
+NCU_DRAM_BYTES_PER_TRIAL = 171_300_000
+NCU_DRAM_SOURCE = "profiles/r01q_launches_ncu.csv (ncu, 26 trials per launch, divided by 26)"
 A_INJ, P0 = 31.4, 7.5e-3
 ZAP_F = np.array([50.0, 100.0, 150.0, 200.0, 250.0], np.float32)  # misc/default_zaplist.txt
 ZAP_W = np.array([0.1, 0.15, 0.15, 0.15, 0.15], np.float32)
@@ -306,7 +311,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
+                         "traffic": NCU_DRAM_BYTES_PER_TRIAL, "traffic_source": NCU_DRAM_SOURCE, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
                          "kernel": "acceleration-trial chain: fft_pass1(resample gather) + fft_pass2 + spectrum + harmonic_peaks",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_TRIAL, "ms_per_launch": chain_ms},
             "candidates_last_step": int(len(merged)) if merged is not None else None,
