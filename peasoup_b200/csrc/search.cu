@@ -198,6 +198,10 @@ __device__ __noinline__ void hp_emit_slow(const float* __restrict__ P, int nbins
   }
 }
 
+}  // namespace ps
+#include "harmonic_smem.cuh"
+namespace ps {
+
 template <int NF, bool FULL>
 __device__ __forceinline__ void hp_chunk(const float* __restrict__ P, int nbins, int base, int lane, const LevelRanges& r,
                                          const LevelScales& ls, float thresh, int acc_idx, const PeakSink& sink) {
@@ -368,6 +372,23 @@ struct ps_search {
   Search impl;
 };
 static Search* SS(ps_search* s) { return reinterpret_cast<Search*>(s); }
+
+// harmonic sums + peaks with TMA-staged operands (harmonic_smem.cuh); spectra must be padded
+template <int NF>
+static int launch_harmonic_smem_nf(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
+  auto k = harmonic_peaks_smem_kernel<NF>;
+  static bool done[64] = {};
+  const size_t smem = sizeof(float) * hs_total(NF) * kHsBufs;
+  int rc = configure_smem(k, smem, s->plan->device, done);
+  if (rc) return rc;
+  PeakSink sink{s->d_peaks, s->d_count, s->cap};
+  const int ntiles = ((int)s->nbins + kHsW - 1) / kHsW;
+  const int work = ntiles * nb, cap = 148 * 3;
+  k<<<work < cap ? work : cap, kHsThreads, smem, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, acc_idx0,
+                                                      sink, ntiles, nb);
+  PS_LAUNCHED("harmonic_peaks_smem_kernel");
+  return PS_OK;
+}
 
 extern "C" {
 
@@ -618,6 +639,16 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
       }
     }
     if (env_skip & 8) continue;
+    static const int env_hsmem = getenv("PS_HSMEM") ? atoi(getenv("PS_HSMEM")) : 1;
+    const int nf = s->prm.nharmonics;
+    if (env_hsmem && nf >= 1 && nf <= 4) {  // the pipeline's own spectra are padded: TMA-staged variant
+      rc = nf == 1 ? launch_harmonic_smem_nf<1>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st)
+         : nf == 2 ? launch_harmonic_smem_nf<2>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st)
+         : nf == 3 ? launch_harmonic_smem_nf<3>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st)
+                   : launch_harmonic_smem_nf<4>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st);
+      if (rc) return rc;
+      continue;
+    }
     if ((rc = launch_harmonic_peaks(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st))) return rc;
   }
   s->last_spectrum = s->d_pbatch + (size_t)(last_nb - 1) * s->pstride;
