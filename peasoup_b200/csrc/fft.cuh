@@ -124,9 +124,10 @@ struct LoadResampled {
     af = afs.v[b];
     af32 = (float)af;
     fsize = (float)size;
-    // float32 evaluation error <= 4e-7*|shift|; a shift estimate this far from a half-integer fixes
-    // the rounding of both samples of a pair
-    thr = 0.5f - (1e-3f + 4e-6f * max_shift + max_step);
+    // float32 evaluation error of the shift: fi and fi - N are exact, so three roundings (the
+    // product, af32 = float(af), the final product) give <= 1.8e-7 |shift| -- 3e-7 with margin.  A
+    // shift estimate this far from a half-integer fixes the rounding of both samples of a pair.
+    thr = 0.5f - (1e-3f + 3e-7f * max_shift + max_step);
     c0 = first;
     n2 = n;
   }
