@@ -20,6 +20,7 @@ c64 = np.complex64
 
 NBINS = 64   # folder.hpp:383-384
 NINTS = 16
+FOLD_CHUNK = 2048   # csrc/fold.cu: samples per partial sum
 
 
 def prev_power_of_two(n):
@@ -43,8 +44,10 @@ def fold_whiten(trial_u8, nsamps, tsamp):
 def fold_series(x, period, tsamp, nbins=NBINS, nints=NINTS):
     """fold_time_series_kernel (kernels.cu:597-633), one block per sub-integration, nbins threads:
     thread t of sub-integration s adds samples s*per + t + nbins*m for m < ceil(per/nbins); the
-    per-bin hit count starts at ONE (so each bin is sum/(hits+1)).  Sums here run in sample order
-    (the reference's shared-memory atomics have no fixed order); reads are clamped to the series."""
+    per-bin hit count starts at ONE (so each bin is sum/(hits+1)).  The reference's shared-memory
+    atomics have no fixed order; the order here is the one csrc/fold.cu uses: chunks of FOLD_CHUNK
+    samples summed in sample order, then the chunk sums added in chunk order (float32 throughout).
+    Reads are clamped to the series."""
     x = np.asarray(x, f32)
     n = len(x)
     per = n // nints
@@ -57,11 +60,12 @@ def fold_series(x, period, tsamp, nbins=NBINS, nints=NINTS):
         frac = np.modf(jj.astype(np.float64) * tsamp_by_period)[0]
         idx = np.floor(frac * nbins).astype(np.int64)
         sums = np.zeros(nbins, f32)
-        # float32 accumulation in sample order
-        for b in range(nbins):
-            sel = x[jj[idx == b]]
-            if len(sel):
-                sums[b] = np.cumsum(sel, dtype=f32)[-1]   # cumsum adds strictly left to right
+        for c0 in range(0, len(jj), FOLD_CHUNK):
+            cj, ci = jj[c0:c0 + FOLD_CHUNK], idx[c0:c0 + FOLD_CHUNK]
+            part = np.zeros(nbins, f32)
+            for b in np.unique(ci):
+                part[b] = np.cumsum(x[cj[ci == b]], dtype=f32)[-1]   # cumsum adds strictly left to right
+            sums = (sums + part).astype(f32)
         count = np.bincount(idx, minlength=nbins).astype(np.int64) + 1
         out[s] = sums / count.astype(f32)
     return out

@@ -10,8 +10,8 @@
 // Difference kept on purpose: the reference's fold kernel zeroes, accumulates (shared-memory
 // atomics) and reads back its phase bins without a barrier between the three steps, so a sample
 // can be lost when the two warps of a block drift apart -- the golden FOLD blocks show it in one
-// or two of the 16 sub-integrations.  fold_kernel here adds every sample, in sample order, so the
-// result is deterministic.
+// or two of the 16 sub-integrations.  The fold here adds every sample in a fixed order (chunks of
+// 2048 samples in sample order, then the chunk sums in order), so the result is deterministic.
 #include <cuComplex.h>
 #include <cmath>
 #include <vector>
@@ -19,40 +19,58 @@
 
 namespace ps {
 
-constexpr int kFoldChunk = 2048;  // samples staged per pass of fold_kernel
+constexpr int kFoldChunk = 2048;  // samples per partial sum
 
-// One CTA per sub-integration.  Samples [s*per, s*per + ceil(per/nbins)*nbins) (what the
-// reference's nbins threads striding by nbins cover, kernels.cu:620-627), clamped to the series.
-// Phase bin = floor(frac(j * tsamp/period) * nbins) in double; out = sum / (hits + 1).
-__global__ void __launch_bounds__(256) fold_kernel(const float* __restrict__ in, float* __restrict__ out, size_t nsamps,
-                                                   size_t per, int nbins, double tsamp_by_period) {
+// Sub-integration s covers samples [s*per, s*per + ceil(per/nbins)*nbins) (what the reference's
+// nbins threads striding by nbins cover, kernels.cu:620-627), clamped to the series.  The order
+// of the additions is fixed: every chunk of kFoldChunk samples is summed per phase bin in sample
+// order (fold_partial_kernel, one CTA per chunk), then the chunk sums of a sub-integration are
+// added in chunk order (fold_finish_kernel).  Phase bin = floor(frac(j * tsamp/period) * nbins)
+// in double; out = sum / (hits + 1).  oracle/fold.py adds in the same order: bit-identical.
+__global__ void __launch_bounds__(256) fold_partial_kernel(const float* __restrict__ in, float* __restrict__ psum,
+                                                           int* __restrict__ pcount, size_t nsamps, size_t per, int nbins,
+                                                           int nchunks, double tsamp_by_period) {
   __shared__ float val[kFoldChunk];
   __shared__ unsigned short bin[kFoldChunk];
-  const size_t first = per * blockIdx.x;
+  const int s = blockIdx.y, chunk = blockIdx.x;
+  const size_t first = per * s;
   size_t last = first + (per + nbins - 1) / nbins * nbins;
   if (last > nsamps) last = nsamps;
-  float sum = 0.f;
-  int count = 1;
-  for (size_t c0 = first; c0 < last; c0 += kFoldChunk) {
-    const int len = (int)((last - c0) < (size_t)kFoldChunk ? (last - c0) : (size_t)kFoldChunk);
-    for (int i = threadIdx.x; i < len; i += blockDim.x) {
-      size_t j = c0 + i;
-      double ip;
-      double fp = modf((double)j * tsamp_by_period, &ip);
-      bin[i] = (unsigned short)__double2int_rd(fp * nbins);
-      val[i] = in[j];
-    }
-    __syncthreads();
-    for (int b = threadIdx.x; b < nbins; b += blockDim.x) {  // nbins <= blockDim: one bin per thread
-      for (int i = 0; i < len; i++)
-        if (bin[i] == b) {
-          sum += val[i];
-          count++;
-        }
-    }
-    __syncthreads();
+  const size_t c0 = first + (size_t)chunk * kFoldChunk;
+  const int len = c0 >= last ? 0 : (int)((last - c0) < (size_t)kFoldChunk ? (last - c0) : (size_t)kFoldChunk);
+  for (int i = threadIdx.x; i < len; i += blockDim.x) {
+    const size_t j = c0 + i;
+    double ip;
+    const double fp = modf((double)j * tsamp_by_period, &ip);
+    bin[i] = (unsigned short)__double2int_rd(fp * nbins);
+    val[i] = in[j];
   }
-  if ((int)threadIdx.x < nbins) out[(size_t)blockIdx.x * nbins + threadIdx.x] = sum / count;
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) {
+    float sum = 0.f;
+    int count = 0;
+    for (int i = 0; i < len; i++)
+      if (bin[i] == b) {
+        sum += val[i];
+        count++;
+      }
+    psum[((size_t)s * nchunks + chunk) * nbins + b] = sum;
+    pcount[((size_t)s * nchunks + chunk) * nbins + b] = count;
+  }
+}
+
+__global__ void fold_finish_kernel(const float* __restrict__ psum, const int* __restrict__ pcount, float* __restrict__ out, int nbins,
+                                   int nchunks) {
+  const int s = blockIdx.x;
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) {
+    float sum = 0.f;
+    int count = 1;  // the reference's hit counter starts at one (kernels.cu:616)
+    for (int c = 0; c < nchunks; c++) {
+      sum += psum[((size_t)s * nchunks + c) * nbins + b];
+      count += pcount[((size_t)s * nchunks + c) * nbins + b];
+    }
+    out[(size_t)s * nbins + b] = sum / count;
+  }
 }
 
 __device__ __forceinline__ int brev(int v, int lg) { return (int)(__brev((unsigned)v) >> (32 - lg)); }
@@ -259,8 +277,22 @@ int ps_fold_timeseries(const float* d_in, float* d_out, size_t nsamps, size_t ns
   if (nbins < 1 || nbins > 256) return invalid("ps_fold_timeseries: nbins must be 1..256");
   if (!nsubints || nsamps < nsubints) return invalid("ps_fold_timeseries: nsamps must be >= nsubints > 0");
   if (!(period > 0)) return invalid("ps_fold_timeseries: period must be positive");
-  fold_kernel<<<(unsigned)nsubints, 256, 0, S(stream)>>>(d_in, d_out, nsamps, nsamps / nsubints, nbins, tsamp / period);
-  PS_LAUNCHED("ps_fold_timeseries");
+  const size_t per = nsamps / nsubints;
+  const size_t span = (per + nbins - 1) / nbins * nbins;
+  const int nchunks = (int)((span + kFoldChunk - 1) / kFoldChunk);
+  if (nsubints > 65535) return invalid("ps_fold_timeseries: too many sub-integrations");
+  cudaStream_t st = S(stream);
+  float* psum = nullptr;  // [nsubints][nchunks][nbins] partial sums, then the same shape of hit counts
+  const size_t cells = nsubints * (size_t)nchunks * nbins;
+  PS_CUDA(cudaMallocAsync(&psum, cells * (sizeof(float) + sizeof(int)), st), "ps_fold_timeseries: scratch");
+  int* pcount = reinterpret_cast<int*>(psum + cells);
+  fold_partial_kernel<<<dim3(nchunks, (unsigned)nsubints), 256, 0, st>>>(d_in, psum, pcount, nsamps, per, nbins, nchunks, tsamp / period);
+  g_launches.fetch_add(1);
+  fold_finish_kernel<<<(unsigned)nsubints, 256, 0, st>>>(psum, pcount, d_out, nbins, nchunks);
+  g_launches.fetch_add(1);
+  cudaError_t e = cudaGetLastError();
+  cudaFreeAsync(psum, st);
+  if (e != cudaSuccess) return cuda_fail(e, "ps_fold_timeseries");
   return PS_OK;
 }
 
