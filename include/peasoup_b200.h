@@ -169,7 +169,10 @@ long ps_search_fetch_peaks(ps_search* s, ps_raw_peak* h_out, size_t max_out, voi
  * PeakFinder::find_candidates, harmonicfolder.hpp:26-38 + peakfinder.hpp:72-94, without
  * materialising the sums): nbatch normalised spectra of size/2+1 bins, `stride` floats apart,
  * spectrum b reported as acceleration index acc_idx0 + b.  Peaks join the handle's peak list
- * (ps_search_reset_peaks / ps_search_fetch_peaks).  Also BASELINE.json configs[2]'s microbench. */
+ * (ps_search_reset_peaks / ps_search_fetch_peaks).  Spectra that are 16-byte aligned, a multiple of
+ * 4 floats apart and followed by >= 4 readable floats each are summed from TMA-staged operands
+ * (harmonic_smem.cuh); any other layout takes the gather kernel.  Same output either way.
+ * Also BASELINE.json configs[2]'s microbench. */
 int ps_search_harmonic_peaks(ps_search* s, const float* d_spectra, size_t stride, int nbatch,
                              int acc_idx0, void* stream);
 /* Diagnostics for stage-by-stage parity tests: device pointers owned by the handle. */

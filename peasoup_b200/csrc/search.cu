@@ -12,6 +12,7 @@
 // peak list: include/peasoup_b200/pipeline.hpp.
 #include <algorithm>
 #include <cmath>
+#include <cstdint>
 #include <cstdlib>
 #include <vector>
 #include "rfft.cuh"
@@ -580,9 +581,19 @@ int ps_search_harmonic_peaks(ps_search* hs, const float* d_spectra, size_t strid
   Search* s = SS(hs);
   if (!s || !d_spectra) return invalid("ps_search_harmonic_peaks: null argument");
   if (nbatch < 0 || stride < s->nbins) return invalid("ps_search_harmonic_peaks: stride must be >= size/2+1");
-  for (int j = 0; j < nbatch; j += 32768) {  // grid.y limit
+  // spectra that are 16-byte aligned and padded by >= 4 floats can take the TMA-staged kernel
+  static const int env_hsmem = getenv("PS_HSMEM") ? atoi(getenv("PS_HSMEM")) : 1;
+  const int nf = s->prm.nharmonics;
+  const bool staged = env_hsmem && nf >= 1 && nf <= 4 && stride % 4 == 0 && stride >= (size_t)s->nbins + 4 &&
+                      (reinterpret_cast<uintptr_t>(d_spectra) & 15u) == 0;
+  for (int j = 0; j < nbatch; j += 32768) {  // grid.y limit of the LDG kernel
     int nb = std::min(32768, nbatch - j);
-    int rc = launch_harmonic_peaks(s, d_spectra + (size_t)j * stride, stride, nb, acc_idx0 + j, S(stream));
+    const float* sp = d_spectra + (size_t)j * stride;
+    int rc = !staged ? launch_harmonic_peaks(s, sp, stride, nb, acc_idx0 + j, S(stream))
+             : nf == 1 ? launch_harmonic_smem_nf<1>(s, sp, stride, nb, acc_idx0 + j, S(stream))
+             : nf == 2 ? launch_harmonic_smem_nf<2>(s, sp, stride, nb, acc_idx0 + j, S(stream))
+             : nf == 3 ? launch_harmonic_smem_nf<3>(s, sp, stride, nb, acc_idx0 + j, S(stream))
+                       : launch_harmonic_smem_nf<4>(s, sp, stride, nb, acc_idx0 + j, S(stream));
     if (rc) return rc;
   }
   return PS_OK;

@@ -274,22 +274,27 @@ def test_full_size_injected_pulsar_properties(lib, oracle):
     assert (got["is_top"] == 0).sum() > 0
 
 
-@pytest.mark.parametrize("size,nbatch", [(1 << 17, 3), (1 << 20, 2)])
-def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch):
+@pytest.mark.parametrize("size,nbatch,pad,nharm", [(1 << 17, 3, 7, 4), (1 << 20, 2, 7, 4), (1 << 17, 3, 64, 4), (1 << 20, 2, 8, 4),
+                                                   (1 << 18, 2, 12, 3), (1 << 18, 2, 4, 2), (1 << 18, 2, 4, 1), (1 << 17, 2, 7, 5)])
+def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch, pad, nharm):
     """ps_search_harmonic_peaks on spectra supplied by the caller (BASELINE.json configs[2]'s stage):
     same bins, same levels and bit-identical S/N as harmonic_sum_kernel + device_find_peaks."""
     tsamp, thresh = 64e-6, 5.0
-    cfg = oracle.SearchConfig(size, tsamp, min_snr=thresh)
+    cfg = oracle.SearchConfig(size, tsamp, nharmonics=nharm, min_snr=thresh)
     rng = np.random.default_rng(size + nbatch)
-    stride = cfg.nbins + 7  # spectra need not be packed
+    # spectra need not be packed: an odd stride takes the gather kernel, a stride that keeps every
+    # spectrum 16-byte aligned with >= 4 floats of padding takes the TMA-staged kernel
+    stride = cfg.nbins + pad
+    stride += (-stride) % 4 if pad % 4 == 0 else 0
     spectra = np.zeros((nbatch, stride), np.float32)
     for b in range(nbatch):
         p = rng.normal(0, 1, cfg.nbins).astype(np.float32)
         p[::32] += 1.0                                        # harmonic_sum_test.cpp's pattern
         f0 = 1000 + 37 * b
         p[f0 * np.arange(1, 17)] += 6.0                       # comb: fundamental + 15 harmonics
+        p[[2047, 2048, 4095, 4096, cfg.nbins - 2, cfg.nbins - 1]] += 40.0   # tile edges of the staged kernel, last bins
         spectra[b, :cfg.nbins] = p
-    s = pb.Search(make_search_params(size, size, tsamp, min_snr=thresh))
+    s = pb.Search(make_search_params(size, size, tsamp, nharm, min_snr=thresh))
     s.reset_peaks()
     d = torch.from_numpy(spectra).cuda()
     s.harmonic_peaks(d, stride, nbatch, acc_idx0=10)
@@ -302,7 +307,11 @@ def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch):
     got = {(int(r["acc_idx"]), int(r["nh"]), int(r["bin"])): np.float32(r["snr"]) for r in peaks}
     assert len(want) > 50 and set(got) == set(want)
     assert all(got[k] == want[k] for k in want)
-    assert any(k[1] == 4 and k[2] == 1000 * 16 for k in got)  # the comb is found at the top level
+    if nharm >= 4:
+        assert any(k[1] == 4 and k[2] == 1000 * 16 for k in got)  # the comb is found at the top level
+    assert any(k[2] == 2048 for k in got)
+    if nharm >= 4:
+        assert any(k[2] == cfg.nbins - 1 for k in got)   # the last bin, alone in the staged kernel's last tile
     s.close()
 
 
