@@ -22,7 +22,7 @@ def relerr(got, want):
     return np.abs(got - want).max() / rms, np.sqrt((np.abs(got - want) ** 2).mean()) / rms
 
 
-@pytest.mark.parametrize("lg", [17, 18, 19, 20, 21, 22, 23])
+@pytest.mark.parametrize("lg", [17, 18, 19, 20, 21, 22, 23, 24, 25])
 def test_r2c_c2r_vs_numpy(lib, lg):
     n = 1 << lg
     rng = np.random.default_rng(lg)
@@ -37,13 +37,15 @@ def test_r2c_c2r_vs_numpy(lib, lg):
     assert emax < TOL_MAX and erms < TOL_RMS, (emax, erms)
     assert X[0].imag == 0 and X[-1].imag == 0
     # u8-like input with a DC term 1e4 x the noise bins: any float32 FFT spreads ~eps*|DC| along the
-    # DC butterfly paths, so only the rms and a 1e-3 max bound (relative to the noise bins) hold
+    # DC butterfly paths, so only the rms and a max bound of 1e-3 (relative to the noise bins) or four
+    # float32 roundings of the DC term, whichever is larger (the DC term grows as n, the noise bins
+    # as sqrt(n): at 2^25 samples the second bound takes over), hold
     xo = (x + 128).astype(np.float32)
     plan.r2c(torch.from_numpy(xo).cuda(), dX)
     Xo = dX.cpu().numpy().view(np.complex64)
     wo = np.fft.rfft(xo.astype(np.float64))
     nrms = np.sqrt((np.abs(wo[1:]) ** 2).mean())
-    assert np.abs(Xo[1:] - wo[1:]).max() / nrms < 1e-3
+    assert np.abs(Xo[1:] - wo[1:]).max() < max(1e-3 * nrms, 4 * 6e-8 * abs(wo[0]))
     assert np.sqrt((np.abs(Xo[1:] - wo[1:]) ** 2).mean()) / nrms < TOL_RMS
     assert abs(Xo[0] - wo[0]) / abs(wo[0]) < 2e-7
     # C2R on an exactly Hermitian spectrum: unnormalised (x n) like cufftExecC2R
