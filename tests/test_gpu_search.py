@@ -316,19 +316,25 @@ def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch, pad
 
 
 @pytest.mark.parametrize("size,acc_hi,a_inj", [(1 << 23, 50.0, 31.4), (1 << 24, 500.0, 312.5)])
-def test_survey_sizes_vs_reference_cuda_build(lib, oracle, ref, size, acc_hi, a_inj):
+def test_survey_sizes_vs_reference_cuda_build(lib, oracle, ref, size, acc_hi, a_inj, tmp_path):
     """BASELINE.json configs[3] and [4] shapes (2^23 samples, +-50 m/s^2; 2^24 samples, +-500 m/s^2)
-    on one DM trial and a handful of accelerations: identical candidates to the unmodified
-    reference build.  At 2^24 samples and 500 m/s^2 the resampling shift reaches ~3700 samples and
+    on one DM trial with the FULL acceleration lists of those configurations (101 and 201 trials):
+    identical candidates to the unmodified reference build.  At 2^24 samples and 500 m/s^2 the resampling shift reaches ~3700 samples and
     crosses a rounding boundary far more often than in the other tests (FP64 fallback of the loader)."""
     tsamp = 64e-6
     nsamps = size + 4096
     trials = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=a_inj, amp=3.0, seed=size % 1000)
-    accs = np.array([0.0, -acc_hi, -acc_hi / 2, a_inj, acc_hi], np.float32)
+    step = 1.0 if acc_hi == 50.0 else 5.0
+    accs = np.sort(np.append(np.arange(-acc_hi, acc_hi + step / 2, step), a_inj)).astype(np.float32)
+    assert len(accs) in (102, 202)
     dms = np.array([12.5], np.float32)
     cfg = oracle.SearchConfig(size, tsamp)
-    want, _ = ref_search(ref, trials, dms, accs, size, nsamps, tsamp)
-    got, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs)
+    zf = tmp_path / "zap.txt"
+    zf.write_text(open(os.path.join(GOLDEN, "default_zaplist.txt")).read())
+    zl = np.loadtxt(zf, dtype=np.float32)
+    want, _ = ref_search(ref, trials, dms, accs, size, nsamps, tsamp, zapfile=str(zf).encode())
+    got, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp, max_peaks=1 << 22), accs=accs,
+                                   zap=(zl[:, 0], zl[:, 1]))
     assert done == len(accs) and len(want) > 5
     compare_candidates(got, want, cfg)
     assert np.any((got["acc"] == np.float32(a_inj)) & (got["snr"] > 20))  # the injected pulsar, at its acceleration
