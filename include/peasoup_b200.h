@@ -165,6 +165,14 @@ int ps_search_accel_batch(ps_search* s, const float* h_acc, int n_acc, int acc_i
  * (acc_idx, nh, bin), i.e. the order the reference's per-spectrum copy_if calls produce). */
 int ps_search_reset_peaks(ps_search* s, void* stream);
 long ps_search_fetch_peaks(ps_search* s, ps_raw_peak* h_out, size_t max_out, void* stream);
+/* After ps_search_fetch_peaks returned PS_EOVERFLOW: the number of records the last batch produced,
+ * and a way to enlarge the device list to hold them (synchronises the device; the list's content is
+ * lost, so the caller resets the peaks and repeats ps_search_accel_batch -- the whitened series is
+ * still there).  The pipeline driver does exactly that, so a DM trial full of interference costs
+ * time instead of failing; the reference silently truncates at 100000 peaks per spectrum
+ * (peakfinder.hpp:59-70). */
+unsigned ps_search_peaks_needed(ps_search* s);
+int ps_search_reserve_peaks(ps_search* s, unsigned max_peaks);
 /* The harmonic-sum + threshold + compaction stage on its own (HarmonicFolder::fold +
  * PeakFinder::find_candidates, harmonicfolder.hpp:26-38 + peakfinder.hpp:72-94, without
  * materialising the sums): nbatch normalised spectra of size/2+1 bins, `stride` floats apart,

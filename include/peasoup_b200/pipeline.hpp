@@ -213,6 +213,17 @@ class Worker {  // pipeline_multi.cu:83-254
     auto finish = [&](Slot& s) {
       clk::time_point t0 = clk::now();
       long n = ps_search_fetch_peaks(s.search, &s.peaks[0], s.peaks.size(), s.stream);
+      for (int attempt = 0; n == PS_EOVERFLOW && attempt < 4; attempt++) {
+        // more above-threshold bins than the list holds (interference): enlarge it and search this DM
+        // trial's accelerations again -- its whitened series is still on the device
+        const size_t want = (size_t)ps_search_peaks_needed(s.search) * 3 / 2 + 1024;
+        if (want > 0x7fffffffu) break;
+        ErrorChecker::check(ps_search_reserve_peaks(s.search, (unsigned)want));
+        s.peaks.resize(want);
+        ErrorChecker::check(ps_search_reset_peaks(s.search, s.stream));
+        ErrorChecker::check(ps_search_accel_batch(s.search, &s.acc_list[0], (int)s.acc_list.size(), 0, s.stream));
+        n = ps_search_fetch_peaks(s.search, &s.peaks[0], s.peaks.size(), s.stream);
+      }
       ErrorChecker::check((int)std::min<long>(n, 0));
       clk::time_point t1 = clk::now();
       t_wait += secs(t0, t1);

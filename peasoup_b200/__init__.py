@@ -66,7 +66,8 @@ SYMBOLS = [
     "ps_running_median", "ps_running_median_noalloc", "ps_divide_c_by_f", "ps_zap_birdies", "ps_rms", "ps_mean", "ps_fill",
     "ps_convert_u8_f32", "ps_fft_plan_create", "ps_fft_plan_destroy", "ps_fft_r2c", "ps_fft_c2r",
     "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
-    "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks",
+    "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks", "ps_search_peaks_needed",
+    "ps_search_reserve_peaks",
     "ps_search_harmonic_peaks", "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
     "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
     "ps_pipeline_run", "ps_pipeline_close", "ps_dedisp_generate_dm_list", "ps_dedisp_max_delay",
@@ -116,6 +117,7 @@ def load() -> C.CDLL:
         "ps_search_whiten": [vp, vp, C.POINTER(f), C.POINTER(f), vp],
         "ps_search_accel_batch": [vp, vp, i, i, vp], "ps_search_reset_peaks": [vp, vp],
         "ps_search_fetch_peaks": [vp, vp, sz, vp],
+        "ps_search_peaks_needed": [vp], "ps_search_reserve_peaks": [vp, u],
         "ps_search_harmonic_peaks": [vp, vp, sz, i, i, vp],
         "ps_search_whitened_series": [vp], "ps_search_last_spectrum": [vp],
         "ps_pipeline_search": [C.POINTER(PipelineParams), vp, vp, i, i, vp, i, vp, vp, i, i, i, vp, C.c_long,
@@ -147,6 +149,7 @@ def load() -> C.CDLL:
     lib.ps_pipeline_profile.argtypes = [C.POINTER(C.c_double)]
     lib.ps_pipeline_profile.restype = None
     lib.ps_search_fetch_peaks.restype = C.c_long
+    lib.ps_search_peaks_needed.restype = C.c_uint
     lib.ps_pipeline_search.restype = C.c_long
     lib.ps_pipeline_run.restype = C.c_long
     lib.ps_search_filterbank.restype = C.c_long

@@ -331,6 +331,7 @@ struct Search {
   ps_raw_peak* d_peaks = nullptr;
   unsigned* d_count = nullptr;
   unsigned cap = 0;
+  unsigned needed = 0;  // record count of the last fetch (ps_search_peaks_needed)
   LevelRanges ranges;
   LevelScales scales;
   float* d_pbatch = nullptr;   // kBatch spectra (stride pstride floats)
@@ -673,6 +674,24 @@ int ps_search_reset_peaks(ps_search* hs, void* stream) {
   return PS_OK;
 }
 
+unsigned ps_search_peaks_needed(ps_search* hs) {
+  Search* s = SS(hs);
+  return s ? s->needed : 0;
+}
+
+int ps_search_reserve_peaks(ps_search* hs, unsigned max_peaks) {
+  Search* s = SS(hs);
+  if (!s) return invalid("ps_search_reserve_peaks: null handle");
+  if (max_peaks <= s->cap) return PS_OK;
+  PS_CUDA(cudaDeviceSynchronize(), "ps_search_reserve_peaks");
+  ps_raw_peak* p = nullptr;
+  PS_CUDA(cudaMalloc(&p, sizeof(ps_raw_peak) * (size_t)max_peaks), "Error from device_malloc");
+  cudaFree(s->d_peaks);
+  s->d_peaks = p;
+  s->cap = max_peaks;
+  return PS_OK;
+}
+
 long ps_search_fetch_peaks(ps_search* hs, ps_raw_peak* h_out, size_t max_out, void* stream) {
   Search* s = SS(hs);
   if (!s) return invalid("ps_search_fetch_peaks: null handle");
@@ -680,6 +699,7 @@ long ps_search_fetch_peaks(ps_search* hs, ps_raw_peak* h_out, size_t max_out, vo
   unsigned count = 0;
   PS_CUDA(cudaMemcpyAsync(&count, s->d_count, sizeof(unsigned), cudaMemcpyDeviceToHost, st), "Error from d2hcpy");
   PS_CUDA(cudaStreamSynchronize(st), "ps_search_fetch_peaks");
+  s->needed = count;
   if (count > s->cap || count > max_out) {
     set_error("ps_search_fetch_peaks: more above-threshold bins than the peak list holds (raise max_peaks)");
     return PS_EOVERFLOW;

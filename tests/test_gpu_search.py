@@ -146,6 +146,19 @@ def test_peak_list_overflow_is_reported(lib):
     s.close()
 
 
+def test_pipeline_grows_a_full_peak_list(lib, oracle):
+    """A DM trial with more above-threshold bins than max_peaks does not fail the pipeline: the list is
+    enlarged and the trial's accelerations are searched again; the result equals a run with a
+    large list.  (The reference truncates silently at 100000 peaks per spectrum.)"""
+    size, tsamp = 1 << 17, 64e-6
+    trials = make_trials(2, size, size, tsamp=tsamp, amp=9.0)
+    accs = np.array([0.0, 12.0, -30.0], np.float32)
+    dms = np.array([3.0, 4.0], np.float32)
+    small, _ = pb.pipeline_search(trials, dms, pipeline_params(size, size, tsamp, min_snr=5.0, max_peaks=64), accs=accs)
+    large, _ = pb.pipeline_search(trials, dms, pipeline_params(size, size, tsamp, min_snr=5.0, max_peaks=1 << 20), accs=accs)
+    assert len(large) > 64 and np.array_equal(small, large)
+
+
 # ------------------------------------------------------------------ pipeline-level
 def test_pipeline_vs_oracle_synthetic(lib, oracle):
     size, nsamps, tsamp = 1 << 17, (1 << 17) + 512, 64e-6
