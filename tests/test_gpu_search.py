@@ -351,3 +351,19 @@ def test_survey_sizes_vs_reference_cuda_build(lib, oracle, ref, size, acc_hi, a_
     assert done == len(accs) and len(want) > 5
     compare_candidates(got, want, cfg)
     assert np.any((got["acc"] == np.float32(a_inj)) & (got["snr"] > 20))  # the injected pulsar, at its acceleration
+
+
+def test_two_workers_on_two_gpus_equal_one(lib):
+    """`-t 2` of the reference (one host thread per GPU, mutex-protected DMDispenser,
+    pipeline_multi.cu:342-359): the merged candidate list equals the one-worker list."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    size, tsamp = 1 << 18, 64e-6
+    ndm = 12
+    trials = make_trials(ndm, size, size, tsamp=tsamp, a_inj=-20.0, amp=9.0)
+    dms = np.linspace(0, 60, ndm).astype(np.float32)
+    accs = np.array([0.0, -20.0, 15.0], np.float32)
+    one, d1 = pb.pipeline_search(trials, dms, pipeline_params(size, size, tsamp), accs=accs, nworkers=1)
+    two, d2 = pb.pipeline_search(trials, dms, pipeline_params(size, size, tsamp), accs=accs, nworkers=2)
+    assert d1 == d2 == ndm * len(accs) and len(one) > 10
+    assert np.array_equal(one, two)   # ps_pipeline_search returns ascending dm_idx order (SURVEY fact 6)
