@@ -9,8 +9,9 @@
 // holds bins base + l + 32 i, so a warp's 32 addresses span < 32 consecutive words: conflict-free,
 // equal addresses broadcast).  The L2 sees sixteen streaming reads instead of 16 scattered 4-byte
 // loads per bin, and the latency of the gathers drops from an L2 round trip to a shared-memory
-// access.  Three 256-thread CTAs (2048-bin tiles) per SM take turns loading and summing; a second
-// staging buffer per CTA (kHsBufs = 2, 1024-bin tiles) was measured slower.
+// access.  Six 128-thread CTAs (1024-bin tiles, 35 KB of staging each) per SM take turns loading
+// and summing (chain us/trial for tiles of 512 / 1024 / 1536 / 2048 bins with 12 / 6 / 4 / 3 CTAs per
+// SM: 58.0 / 55.4 / 56.2 / 57.0); a second staging buffer per CTA (kHsBufs = 2) was measured slower.
 //
 // Both harmonic kernels pull 8.5 words per bin out of the L2 and run close to its throughput cap
 // (143 MB per 2^22-bin spectrum in 14.1 us = 10 TB/s against ~12 TB/s); this one is ~5 % faster
@@ -25,7 +26,8 @@
 
 namespace ps {
 
-constexpr int kHsW = 2048;   // output bins per tile; W/8 threads (8 bins per lane)
+constexpr int kHsW = 1024;   // output bins per tile; W/8 threads (8 bins per lane)
+constexpr int kHsCtas = 6;   // CTAs per SM (35 KB of staging and 10k registers each): enough tiles in flight to hide the copies
 constexpr int kHsBufs = 1;   // staging buffers per CTA (2 = the next tile's copies fly while this one is summed)
 
 // fractions in the accumulation order of hp_chunk: index, numerator, shift
@@ -57,7 +59,7 @@ __device__ const int c_hs_off[15] = {hs_offset(0), hs_offset(1), hs_offset(2),  
 __device__ __forceinline__ int hs_p(int k, int m, int s) { return (int)(((long long)k * m + (1 << (s - 1))) >> s); }
 
 template <int NF>
-__global__ void __launch_bounds__(kHsThreads, 3) harmonic_peaks_smem_kernel(const float* __restrict__ Pall, int nbins, size_t pstride,
+__global__ void __launch_bounds__(kHsThreads, kHsCtas) harmonic_peaks_smem_kernel(const float* __restrict__ Pall, int nbins, size_t pstride,
                                                                             LevelRanges r, LevelScales ls, float thresh, int acc_idx0,
                                                                             PeakSink sink, int ntiles, int nbatch) {
   static_assert(NF >= 1 && NF <= 4, "shared-memory staging is sized for up to 4 folds");

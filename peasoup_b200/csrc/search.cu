@@ -385,7 +385,7 @@ static int launch_harmonic_smem_nf(Search* s, const float* d_spectra, size_t str
   if (rc) return rc;
   PeakSink sink{s->d_peaks, s->d_count, s->cap};
   const int ntiles = ((int)s->nbins + kHsW - 1) / kHsW;
-  const int work = ntiles * nb, cap = 148 * 3;
+  const int work = ntiles * nb, cap = 148 * kHsCtas;
   k<<<work < cap ? work : cap, kHsThreads, smem, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, acc_idx0,
                                                       sink, ntiles, nb);
   PS_LAUNCHED("harmonic_peaks_smem_kernel");
