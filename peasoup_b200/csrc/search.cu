@@ -307,6 +307,86 @@ __global__ void u8_mean_finalize_kernel(unsigned long long* acc, float n, float*
   acc[0] = 0;
 }
 
+// ---- per-DM whitening, fused passes (the staged entry points keep one kernel per reference call)
+// Z (packed transform) -> X (Hermitian bins, r2c_post_kernel's arithmetic) and |X| (kernels.cu:215-227)
+// in one pass: the median filter needs |X|, the de-reddening needs X.
+__global__ void __launch_bounds__(256) whiten_split_power_kernel(const float2* __restrict__ Z, float2* __restrict__ X,
+                                                                 float* __restrict__ pspec, unsigned M) {
+  for (unsigned k = blockIdx.x * blockDim.x + threadIdx.x; k <= M; k += gridDim.x * blockDim.x) {
+    const float2 zk = Z[k == M ? 0 : k];
+    const float2 zm = Z[k == 0 || k == M ? 0 : M - k];
+    float wr, wi;
+    sincospif((float)k / (float)M, &wi, &wr);  // W_N^k = (cos, -sin)(pi k/M)
+    const float2 x = split_bin(zk, zm, make_float2(wr, -wi));
+    X[k] = x;
+    pspec[k] = amplitude_rsqrt(x.x, x.y);
+  }
+}
+
+// zapping (kernels.cu:1036-1069) expressed on the MEDIAN: a negative median marks a zapped bin, and
+// whiten_deredden_stats_kernel writes (1, 0) there.  One warp per birdie.
+__global__ void zap_mark_kernel(float* __restrict__ median, const float* __restrict__ birdies, const float* __restrict__ widths,
+                                float bin_width, unsigned nbirdies, unsigned nbins) {
+  unsigned w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= nbirdies) return;
+  int lo, hi;
+  if (!zap_range(birdies[w], widths[w], bin_width, nbins, &lo, &hi)) return;
+  for (int i = lo + (int)lane; i < hi; i += 32) median[i] = -1.0f;
+}
+
+__device__ __forceinline__ float2 whitened_bin(const float2* __restrict__ X, const float* __restrict__ median, unsigned i) {
+  const float m = median[i];
+  if (m < 0.f) return make_float2(1.f, 0.f);       // zapped
+  return deredden_value(X[i], m, i);               // bins 0-4 zeroed, the rest divided by the median
+}
+
+// de-redden + zap + interbinned amplitude + its sum and sum of squares (dereddener.hpp:64-66,
+// birdiezapper.hpp, spectrumformer.hpp:8-14, stats.hpp:25-33) in one pass: the whitened spectrum is
+// written once (to Xw, read by the C2R), the interbinned spectrum is only needed for its mean and
+// standard deviation and is never stored.  Four bins per thread + the left neighbour.
+__global__ void __launch_bounds__(256) whiten_deredden_stats_kernel(const float2* __restrict__ X, const float* __restrict__ median,
+                                                                    float2* __restrict__ Xw, unsigned nbins,
+                                                                    double* __restrict__ partials) {
+  double s = 0.0, q = 0.0;
+  const unsigned ngroups = (nbins + 3) / 4;
+  for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+    const unsigned i0 = 4 * g;
+    float2 left = i0 ? whitened_bin(X, median, i0 - 1) : make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const unsigned i = i0 + j;
+      if (i < nbins) {
+        const float2 x = whitened_bin(X, median, i);
+        Xw[i] = x;
+        const double v = interbin_amplitude(x.x, x.y, left.x, left.y);
+        s += v;
+        q += v * v;
+        left = x;
+      }
+    }
+  }
+  __shared__ double sh[2][8];
+  for (int o = 16; o; o >>= 1) {
+    s += __shfl_down_sync(0xffffffffu, s, o);
+    q += __shfl_down_sync(0xffffffffu, q, o);
+  }
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    sh[0][w] = s;
+    sh[1][w] = q;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0, b = 0;
+    for (int i = 0; i < 8; i++) {
+      a += sh[0][i];
+      b += sh[1][i];
+    }
+    partials[2 * blockIdx.x] = a;
+    partials[2 * blockIdx.x + 1] = b;
+  }
+}
+
 struct Search {
   ps_search_params prm;
   ps_fft_plan_t* plan = nullptr;
@@ -505,18 +585,27 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   if ((rc = launch_pass1<false>(p, ld, st))) return rc;
   StoreNatural sn{reinterpret_cast<float2*>(p->Z), 0, 0, 0, nullptr};
   if ((rc = launch_pass2<false>(p, sn, st))) return rc;
-  if ((rc = launch_r2c_post(p, p->Z, s->d_X, st))) return rc;
-  if ((rc = ps_form_power_series((const ps_complex*)s->d_X, s->d_pspec, s->nbins, 0, st))) return rc;
+  // X and |X| in one pass, running median, then de-redden + zap + interbin + stats in one pass; the
+  // whitened spectrum goes to the plan's Z buffer (free here: X still holds the unwhitened bins)
+  whiten_split_power_kernel<<<ew_grid(p->M + 1, 256, 2), 256, 0, st>>>(reinterpret_cast<const float2*>(p->Z), s->d_X, s->d_pspec, p->M);
+  PS_LAUNCHED("whiten_split_power_kernel");
   if ((rc = launch_running_median(s->d_pspec, s->nbins, s->bin_width, s->prm.boundary_5_freq, s->prm.boundary_25_freq,
                                   s->d_median, s->d_work, st)))
     return rc;
-  if ((rc = ps_divide_c_by_f((ps_complex*)s->d_X, s->d_median, s->nbins, st))) return rc;
-  if (s->nbirdies)
-    if ((rc = ps_zap_birdies((ps_complex*)s->d_X, s->d_birdies, s->d_widths, s->bin_width_f, s->nbirdies, s->nbins, st)))
-      return rc;
-  if ((rc = ps_form_power_series((const ps_complex*)s->d_X, s->d_pspec, s->nbins, 1, st))) return rc;
-  if ((rc = launch_stats(s->d_pspec, s->nbins, s->d_partials, s->d_stats, st))) return rc;
-  LoadC2RPre lc{s->d_X, p->M, p->n2, 0};
+  if (s->nbirdies) {
+    const unsigned threads = 128, blocks = (s->nbirdies * 32 + threads - 1) / threads;
+    zap_mark_kernel<<<blocks, threads, 0, st>>>(s->d_median, s->d_birdies, s->d_widths, s->bin_width_f, s->nbirdies, s->nbins);
+    PS_LAUNCHED("zap_mark_kernel");
+  }
+  float2* Xw = reinterpret_cast<float2*>(p->Z);
+  {
+    unsigned g = ew_grid((s->nbins + 3) / 4, 256, 2);
+    if (g > kMaxStatParts) g = kMaxStatParts;
+    whiten_deredden_stats_kernel<<<g, 256, 0, st>>>(s->d_X, s->d_median, Xw, s->nbins, s->d_partials);
+    PS_LAUNCHED("whiten_deredden_stats_kernel");
+    if ((rc = launch_finalize_stats(s->d_partials, (int)g, s->nbins, s->d_stats, st))) return rc;
+  }
+  LoadC2RPre lc{Xw, p->M, p->n2, 0};
   if ((rc = launch_pass1<true>(p, lc, st))) return rc;
   StoreTransposedPairs so{reinterpret_cast<float2*>(s->d_tim), 0, 0, s->lg_n2, s->col_len};
   if ((rc = launch_pass2<true>(p, so, st))) return rc;

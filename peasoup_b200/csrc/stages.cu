@@ -217,13 +217,17 @@ int launch_sums(const float* d, size_t n, double* d_partials, int* nparts, cudaS
   return PS_OK;
 }
 
+int launch_finalize_stats(const double* d_partials, int nparts, size_t n, float* d_out3, cudaStream_t st) {
+  finalize_stats_kernel<<<1, 256, 0, st>>>(d_partials, nparts, (float)(int)n, d_out3);
+  PS_LAUNCHED("finalize_stats_kernel");
+  return PS_OK;
+}
+
 int launch_stats(const float* d, size_t n, double* d_partials, float* d_out3, cudaStream_t st) {
   int np = 0;
   int rc = launch_sums(d, n, d_partials, &np, st);
   if (rc) return rc;
-  finalize_stats_kernel<<<1, 256, 0, st>>>(d_partials, np, (float)(int)n, d_out3);
-  PS_LAUNCHED("finalize_stats_kernel");
-  return PS_OK;
+  return launch_finalize_stats(d_partials, np, n, d_out3, st);
 }
 
 int launch_running_median(const float* d_pspec, unsigned nbins, double bin_width, float b5, float b25, float* d_median,

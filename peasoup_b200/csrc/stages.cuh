@@ -15,6 +15,8 @@ constexpr unsigned kMaxStatParts = 1184;  // 148 SMs x 8 blocks
 double accel_fact(float a, float tsamp);
 int launch_sums(const float* d, size_t n, double* d_partials, int* nparts, cudaStream_t st);
 int launch_stats(const float* d, size_t n, double* d_partials, float* d_out3, cudaStream_t st);
+// second half of launch_stats: {mean, rms, std} of n values from nparts (sum, sum of squares) pairs
+int launch_finalize_stats(const double* d_partials, int nparts, size_t n, float* d_out3, cudaStream_t st);
 int launch_running_median(const float* d_pspec, unsigned nbins, double bin_width, float b5, float b25, float* d_median,
                           float* d_work, cudaStream_t st);
 
