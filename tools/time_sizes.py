@@ -7,11 +7,12 @@ from peasoup_b200.host import make_search_params
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from synth import make_trials
 torch.cuda.set_device(0)
-for lg, amax, nacc in ((22, 50.0, 101), (23, 50.0, 101), (24, 500.0, 201)):
+for lg, amax, nacc, nfolds in ((20, 50.0, 101, 4), (21, 50.0, 101, 4), (22, 50.0, 101, 4), (23, 50.0, 101, 4), (23, 500.0, 201, 4),
+                               (23, 50.0, 101, 5), (23, 50.0, 101, 3), (24, 500.0, 201, 4)):
     size, tsamp = 1 << lg, 64e-6
     trials = make_trials(1, size + 4096, size, tsamp=tsamp, a_inj=amax * 0.6, amp=3.0, seed=lg)
     accs = np.linspace(-amax, amax, nacc).astype(np.float32)
-    s = pb.Search(make_search_params(size, size + 4096, tsamp, 4, 9.0))
+    s = pb.Search(make_search_params(size, size + 4096, tsamp, nfolds, 9.0))
     st = torch.cuda.Stream()
     d = torch.from_numpy(trials[0]).cuda()
     s.whiten(d, stream=st); s.reset_peaks(stream=st); s.accel_batch(accs[:40], stream=st); st.synchronize()
@@ -22,5 +23,5 @@ for lg, amax, nacc in ((22, 50.0, 101), (23, 50.0, 101), (24, 500.0, 201)):
         e0.record(st); s.accel_batch(accs, stream=st); e1.record(st); st.synchronize()
         best = min(best, e0.elapsed_time(e1) / len(accs))
     gbs = 16.0 * size / (best * 1e-3) / 1e9
-    print(f"2^{lg} samples, {nacc} accelerations +-{amax:g}: {best*1e3:.1f} us/trial, {gbs:.0f} GB/s on 16N bytes ({gbs/6546.9:.3f} of 6546.9)")
+    print(f"2^{lg} samples, {nacc} accelerations +-{amax:g}, {nfolds} folds: {best*1e3:.1f} us/trial, {gbs:.0f} GB/s on 16N bytes ({gbs/6546.9:.3f} of 6546.9)")
     s.close()
