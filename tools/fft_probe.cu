@@ -124,7 +124,7 @@ void run1(const char* name, LoadResampled ld, cf* Yt, FftTables t, int n1, int n
 }
 
 int main() {
-  const int n1 = 2048, n2 = 2048, nbatch = 2;
+  const int n1 = 2048, n2 = 2048, nbatch = 8;
   const size_t M = (size_t)n1 * n2;
   cf *Yt, *Z, *W, *TA, *TB;
   cudaMalloc(&Yt, sizeof(cf) * M * nbatch); cudaMalloc(&Z, sizeof(cf) * M * nbatch);
@@ -156,6 +156,14 @@ int main() {
     run1<0>("full", ld, Yt, t, n1, n2, nbatch);
     run1<1>("noload", ld, Yt, t, n1, n2, nbatch);
     run1<2>("nostore", ld, Yt, t, n1, n2, nbatch);
+    LoadResampled hot = ld;
+    hot.n1 = 0;  // every pair address collapses to its row index: the loads stay in a 16 KB region (index math kept, memory cheap)
+    run1<0>("hotload", hot, Yt, t, n1, n2, nbatch);
+    run1<2>("hot+nostore", hot, Yt, t, n1, n2, nbatch);
+    LoadResampled zero = ld;
+    for (int b = 0; b < 8; b++) zero.afs.v[b] = 0.0;  // no shift: every pair is one aligned 8-byte load
+    zero.max_shift = 0.f; zero.max_step = 0.f;
+    run1<0>("acc0", zero, Yt, t, n1, n2, nbatch);
   }
   return 0;
 }
