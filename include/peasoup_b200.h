@@ -117,7 +117,8 @@ int ps_convert_u8_f32(const unsigned char* d_in, float* d_out, unsigned n, void*
 
 /* ---------------- FFT (replaces cuFFT, ffter.hpp:46-78) ------------------------------- */
 typedef struct ps_fft_plan ps_fft_plan;
-/* cufftPlan1d(&plan, n, CUFFT_R2C/C2R, 1): n a power of two, 2^17 <= n <= 2^25. */
+/* cufftPlan1d(&plan, n, CUFFT_R2C/C2R, 1): powers of two 2^17..2^25 run on the two-pass engine, any
+ * other n in [2, 2^24] as a chirp-z convolution on top of it (bluestein.cu). */
 int ps_fft_plan_create(unsigned n, ps_fft_plan** out);
 void ps_fft_plan_destroy(ps_fft_plan* plan);
 /* cufftExecR2C: n floats -> n/2+1 complex, unnormalised. */

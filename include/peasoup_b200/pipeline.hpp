@@ -155,7 +155,81 @@ class Worker {  // pipeline_multi.cu:83-254
     return prm;
   }
 
+  // transform lengths the fused device path takes (fft.cu: two-pass engine)
+  static bool fused_size(unsigned int n) { return n >= (1u << 17) && n <= (1u << 25) && !(n & (n - 1)); }
+
+  // Any other length (--fft_size smaller than 2^17 or not a power of two): the loop of
+  // pipeline_multi.cu:145-244 statement by statement on the staged entry points -- one kernel per
+  // reference call, transforms through the chirp-z path of ps_fft_*.  Slower, same candidates.
+  void start_staged() {
+    ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
+    const unsigned nsamps = trials.get_nsamps();
+    ReusableDeviceTimeSeries<float, unsigned char> d_tim(size);
+    DeviceTimeSeries<float> d_tim_r(size);
+    TimeDomainResampler resampler;
+    float tobs = size * trials.get_tsamp();
+    float bin_width = 1.0 / tobs;
+    DeviceFourierSeries<cufftComplex_t> d_fseries(size / 2 + 1, bin_width);
+    DevicePowerSpectrum<float> pspec(d_fseries);
+    std::vector<float> zf = args.zap_freqs, zw = args.zap_widths;
+    if (args.zapfilename != "") Zapper::parse(args.zapfilename, zf, zw);
+    Zapper bzap(zf, zw);
+    Dereddener rednoise(size / 2 + 1);
+    SpectrumFormer former;
+    PeakFinder cand_finder(args.min_snr, args.min_freq, args.max_freq, size);
+    HarmonicSums<float> sums(pspec, args.nharmonics);
+    HarmonicFolder harm_folder(sums);
+    HarmonicDistiller harm_finder(args.freq_tol, args.max_harm, false);
+    AccelerationDistiller acc_still(tobs, args.freq_tol, true);
+    FFTerR2C r2cfft(size);
+    FFTerC2R c2rfft(size);
+    std::vector<float> acc_list;
+    float mean, std, rms;
+    DedispersedTimeSeries<unsigned char> tim;
+    while (true) {
+      int ii = manager.get_dm_trial_idx();
+      if (ii == -1) break;
+      trials.get_idx(ii, tim);
+      d_tim.copy_from_host(tim);
+      if (size > nsamps) {  // pad with the mean of the valid samples, :160-163
+        float pad = stats::mean<float>(d_tim.get_data(), nsamps);
+        d_tim.fill(nsamps, size, pad);
+      }
+      r2cfft.execute(d_tim.get_data(), d_fseries.get_data());
+      former.form(d_fseries, pspec);
+      rednoise.calculate_median(pspec);
+      rednoise.deredden(d_fseries);
+      if (!zf.empty()) bzap.zap(d_fseries);
+      former.form_interpolated(d_fseries, pspec);
+      stats::stats<float>(pspec.get_data(), size / 2 + 1, &mean, &rms, &std);
+      c2rfft.execute(d_fseries.get_data(), d_tim.get_data());
+      if (fixed_accs)
+        acc_list = *fixed_accs;
+      else
+        acc_plan.generate_accel_list(tim.get_dm(), acc_list);
+      CandidateCollection accel_trial_cands;
+      for (size_t jj = 0; jj < acc_list.size(); jj++) {
+        resampler.resampleII(d_tim, d_tim_r, size, acc_list[jj]);
+        r2cfft.execute(d_tim_r.get_data(), d_fseries.get_data());
+        former.form_interpolated(d_fseries, pspec);
+        stats::normalise(pspec.get_data(), mean * size, std * size, size / 2 + 1);
+        harm_folder.fold(pspec);
+        SpectrumCandidates trial_cands(tim.get_dm(), ii + dm_idx_offset, acc_list[jj]);
+        cand_finder.find_candidates(pspec, trial_cands);
+        cand_finder.find_candidates(sums, trial_cands);
+        accel_trial_cands.append(harm_finder.distill(trial_cands.cands));
+      }
+      dm_trial_cands.append(acc_still.distill(accel_trial_cands.cands));
+      trials_done += acc_list.size();
+    }
+    ErrorChecker::check_cuda_error(cudaDeviceSynchronize(), "Worker::start_staged");
+  }
+
   void start() {
+    if (!fused_size(size) || (getenv("PS_STAGED") && atoi(getenv("PS_STAGED")) == 1)) {  // PS_STAGED=1: tests
+      start_staged();
+      return;
+    }
     ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
     ps_search_params prm = search_params(args, size, trials.get_nsamps(), trials.get_tsamp());
 

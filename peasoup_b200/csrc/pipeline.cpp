@@ -71,7 +71,9 @@ int ps_pipeline_open(const ps_pipeline_params* p, const float* h_zap_freqs, cons
     }
     h->size = args.size ? args.size : Utils::prev_power_of_two(p->search.nsamps);
     ps_search_params sp = Worker::search_params(args, h->size, p->search.nsamps, p->search.tsamp);
-    for (int i = 0; i < nworkers; i++) h->slots.push_back(new WorkerSlots(device0 + i, sp, args.zap_freqs, args.zap_widths));
+    // (other transform lengths run Worker::start_staged, which owns its device objects)
+    for (int i = 0; i < nworkers; i++)
+      h->slots.push_back(Worker::fused_size(h->size) ? new WorkerSlots(device0 + i, sp, args.zap_freqs, args.zap_widths) : nullptr);
     *out = h;
     return PS_OK;
   } catch (std::exception& e) {

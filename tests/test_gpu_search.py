@@ -208,6 +208,41 @@ def test_pipeline_vs_oracle_synthetic(lib, oracle):
     assert np.all(np.diff(got["dm_idx"]) >= 0) and got["is_top"][0] == 1
 
 
+@pytest.mark.parametrize("size,nsamps", [(1 << 16, (1 << 16) + 300), (100000, 120000), (1 << 15, 30000)])
+def test_pipeline_other_transform_lengths_vs_oracle(lib, oracle, size, nsamps):
+    """--fft_size below 2^17 or not a power of two (cuFFT takes any length): the pipeline falls back to
+    the reference's statement-by-statement loop on the staged entry points (Worker::start_staged,
+    chirp-z transforms) and finds the same candidates as the oracle.  The last case pads with the mean."""
+    tsamp = 64e-6
+    ndm = 3
+    trials = make_trials(ndm, nsamps, size, tsamp=tsamp, a_inj=31.4, amp=12.0)
+    dms = np.linspace(0, 20, ndm).astype(np.float32)
+    accs = np.array([0.0, -50.0, 31.4], np.float32)
+    zl = np.loadtxt(os.path.join(GOLDEN, "default_zaplist.txt"), dtype=np.float32)
+    cfg = oracle.SearchConfig(size, tsamp, zap=(zl[:, 0], zl[:, 1]))
+    got, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs, zap=(zl[:, 0], zl[:, 1]))
+    assert done == ndm * len(accs)
+    want = oracle.search(trials, dms, accs, cfg)
+    assert len(want) > 5
+    compare_candidates(got, want, cfg)
+
+
+def test_pipeline_staged_loop_equals_fused_loop(lib, monkeypatch):
+    """PS_STAGED=1 sends a power-of-two size through Worker::start_staged: the same records as the
+    fused kernels (S/N to 1e-4: the staged loop normalises and sums in separate kernels)."""
+    size, nsamps, tsamp = 1 << 17, (1 << 17) + 512, 0.00032
+    trials = make_trials(4, nsamps, size, tsamp=tsamp, a_inj=31.4, amp=9.0)
+    dms = np.linspace(0, 30, 4).astype(np.float32)
+    accs = np.array([0.0, -50.0, 31.4, 50.0], np.float32)
+    fused, _ = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs)
+    monkeypatch.setenv("PS_STAGED", "1")
+    staged, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp), accs=accs)
+    assert done == 16 and len(staged) == len(fused) > 20
+    for k in ("dm_idx", "acc", "nh", "is_top", "freq"):
+        assert np.array_equal(staged[k], fused[k]), k
+    assert np.allclose(staged["snr"], fused["snr"], rtol=1e-4)
+
+
 def test_pipeline_acceleration_plan_and_empty(lib, oracle):
     size, tsamp = 1 << 17, 0.00032
     trials = make_trials(2, size + 10, size, tsamp=tsamp, a_inj=0.0, p0=0.1, amp=6.0, birdies=False)
