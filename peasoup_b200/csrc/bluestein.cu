@@ -18,7 +18,37 @@ struct Bluestein {
   float2* B = nullptr;      // spectrum of the wrapped conj chirp, M/2+1 bins (b is even: B_{M-k} = B_k)
   float *ar = nullptr, *ai = nullptr;    // M reals each: convolution input, then output
   float2 *SA = nullptr, *SB = nullptr;   // M/2+1 bins each
+  double* part = nullptr;   // kMeanParts partial sums of the R2C input
+  float* mean = nullptr;    // its mean: taken out before the convolution, put back into bin 0
 };
+constexpr int kMeanParts = 256;
+
+// The rounding error of the convolution scales with the norm of its input, DC included; 8-bit
+// samples sit on a mean of ~8 sigma.  A constant only feeds bin 0 of a length-n transform, so the
+// mean is subtracted here and n * mean added to X_0 afterwards.  Fixed grid, fixed order.
+__global__ void __launch_bounds__(256) partial_sums_kernel(const float* __restrict__ x, unsigned n, double* __restrict__ part) {
+  __shared__ double sh[256];
+  double acc = 0.0;
+  for (unsigned k = blockIdx.x * 256 + threadIdx.x; k < n; k += gridDim.x * 256) acc += (double)x[k];
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
+}
+
+__global__ void __launch_bounds__(kMeanParts) mean_kernel(const double* __restrict__ part, unsigned n, float* __restrict__ mean) {
+  __shared__ double sh[kMeanParts];
+  sh[threadIdx.x] = part[threadIdx.x];
+  __syncthreads();
+  for (int s = kMeanParts / 2; s > 0; s >>= 1) {
+    if ((int)threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *mean = (float)(sh[0] / (double)n);
+}
 
 // w_k = exp(-i pi (k^2 mod 2n) / n): the phase is reduced in integers, evaluated in double
 __global__ void chirp_kernel(float2* __restrict__ w, unsigned n) {
@@ -48,13 +78,14 @@ __global__ void merge_spectra_kernel(float2* __restrict__ B, const float2* __res
   }
 }
 
-// a_k = x_k w_k (real input), zero padded to M
+// a_k = (x_k - mean) w_k (real input), zero padded to M
 __global__ void pre_real_kernel(const float* __restrict__ x, const float2* __restrict__ w, float* __restrict__ ar, float* __restrict__ ai,
-                                unsigned n, unsigned M) {
+                                unsigned n, unsigned M, const float* __restrict__ mean) {
+  const float mu = *mean;
   for (unsigned k = blockIdx.x * blockDim.x + threadIdx.x; k < M; k += gridDim.x * blockDim.x) {
     float r = 0.f, i = 0.f;
     if (k < n) {
-      float v = x[k];
+      float v = x[k] - mu;
       float2 c = w[k];
       r = v * c.x;
       i = v * c.y;
@@ -97,13 +128,15 @@ __global__ void convolve_kernel(float2* __restrict__ SA, float2* __restrict__ SB
   }
 }
 
-// X_j = w_j (cr_j + i ci_j) / M
+// X_j = w_j (cr_j + i ci_j) / M, and the mean taken out by pre_real_kernel back into X_0
 __global__ void post_complex_kernel(const float* __restrict__ cr, const float* __restrict__ ci, const float2* __restrict__ w,
-                                    float2* __restrict__ X, unsigned count, float scale) {
+                                    float2* __restrict__ X, unsigned count, float scale, const float* __restrict__ mean, unsigned n) {
   for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) {
     float2 c = w[j];
     float r = cr[j] * scale, i = ci[j] * scale;
-    X[j] = make_float2(r * c.x - i * c.y, r * c.y + i * c.x);
+    float2 v = make_float2(r * c.x - i * c.y, r * c.y + i * c.x);
+    if (j == 0) v.x = (float)((double)v.x + (double)n * (double)*mean);
+    X[j] = v;
   }
 }
 
@@ -117,7 +150,7 @@ __global__ void post_real_kernel(const float* __restrict__ cr, const float* __re
 
 void bluestein_destroy(Bluestein* b) {
   if (!b) return;
-  cudaFree(b->w); cudaFree(b->B); cudaFree(b->ar); cudaFree(b->ai); cudaFree(b->SA); cudaFree(b->SB);
+  cudaFree(b->w); cudaFree(b->B); cudaFree(b->ar); cudaFree(b->ai); cudaFree(b->SA); cudaFree(b->SB); cudaFree(b->part); cudaFree(b->mean);
   delete b;
 }
 
@@ -150,6 +183,8 @@ int bluestein_create(unsigned n, const ps_fft_plan_t* core, Bluestein** out) {
   if (e == cudaSuccess) e = cudaMalloc(&b->ai, sizeof(float) * b->M);
   if (e == cudaSuccess) e = cudaMalloc(&b->SA, sizeof(float2) * nb);
   if (e == cudaSuccess) e = cudaMalloc(&b->SB, sizeof(float2) * nb);
+  if (e == cudaSuccess) e = cudaMalloc(&b->part, sizeof(double) * kMeanParts);
+  if (e == cudaSuccess) e = cudaMalloc(&b->mean, sizeof(float));
   if (e != cudaSuccess) {
     bluestein_destroy(b);
     return cuda_fail(e, "Error from device_malloc");
@@ -175,12 +210,17 @@ int bluestein_create(unsigned n, const ps_fft_plan_t* core, Bluestein** out) {
 }
 
 int bluestein_r2c(const Bluestein* b, const ps_fft_plan_t* core, const float* d_in, float2* d_out, cudaStream_t st) {
-  pre_real_kernel<<<ew_grid(b->M, 256), 256, 0, st>>>(d_in, b->w, b->ar, b->ai, b->n, b->M);
+  partial_sums_kernel<<<kMeanParts, 256, 0, st>>>(d_in, b->n, b->part);
+  PS_LAUNCHED("bluestein: partial sums");
+  mean_kernel<<<1, kMeanParts, 0, st>>>(b->part, b->n, b->mean);
+  PS_LAUNCHED("bluestein: mean");
+  pre_real_kernel<<<ew_grid(b->M, 256), 256, 0, st>>>(d_in, b->w, b->ar, b->ai, b->n, b->M, b->mean);
   PS_LAUNCHED("bluestein: pre");
   int rc = convolve(b, core, st);
   if (rc) return rc;
   // the two C2Rs are unnormalised (x M)
-  post_complex_kernel<<<ew_grid(b->n / 2 + 1, 256), 256, 0, st>>>(b->ar, b->ai, b->w, d_out, b->n / 2 + 1, 1.0f / (float)b->M);
+  post_complex_kernel<<<ew_grid(b->n / 2 + 1, 256), 256, 0, st>>>(b->ar, b->ai, b->w, d_out, b->n / 2 + 1, 1.0f / (float)b->M, b->mean,
+                                                                  b->n);
   PS_LAUNCHED("bluestein: post");
   return PS_OK;
 }

@@ -145,14 +145,16 @@ def test_arbitrary_length_vs_numpy(lib, n):
     want = np.fft.rfft(x.astype(np.float64))
     emax, erms = relerr(X, want)
     assert emax < 5e-5 and erms < 5e-6, (emax, erms)
-    # u8-like input (large DC): the chirp spreads the DC term over the whole convolution
+    # u8-like input (large DC): the mean is taken out before the convolution and put back into
+    # bin 0, so the other bins are as accurate as for zero-mean input
     xo = (x + 128).astype(np.float32)
     plan.r2c(torch.from_numpy(xo).cuda(), dX)
     Xo = dX.cpu().numpy().view(np.complex64)
     wo = np.fft.rfft(xo.astype(np.float64))
     nrms = np.sqrt((np.abs(wo[1:]) ** 2).mean())
-    assert np.sqrt((np.abs(Xo[1:] - wo[1:]) ** 2).mean()) / nrms < 1e-4
-    assert abs(Xo[0] - wo[0]) / abs(wo[0]) < 1e-5
+    assert np.sqrt((np.abs(Xo[1:] - wo[1:]) ** 2).mean()) / nrms < 5e-6
+    assert np.abs(Xo[1:] - wo[1:]).max() / nrms < 5e-5
+    assert abs(Xo[0] - wo[0]) / abs(wo[0]) < 1e-6
     # C2R, unnormalised
     Xc = want.astype(np.complex64)
     dy = torch.zeros(n, dtype=torch.float32, device="cuda")
