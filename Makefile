@@ -2,7 +2,7 @@
 # Test infrastructure (CPU oracle, reference harness) is built by oracle/Makefile.
 NVCC ?= nvcc
 ARCH := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function -Iinclude
+NVFLAGS := $(ARCH) $(EXTRA) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function -Iinclude
 CSRC := peasoup_b200/csrc
 LIB := peasoup_b200/lib/libpeasoup_b200.so
 OBJS := build/stages.o build/fft.o build/bluestein.o build/search.o build/dedisp.o build/fold.o build/coincidence.o build/pipeline.o
