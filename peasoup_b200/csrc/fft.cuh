@@ -120,6 +120,8 @@ struct LoadResampled {
   double af;
   float af32, fsize, thr;
   int n2, c0;
+  unsigned col_mask;
+  unsigned i_limit;  // host: sample indices below this take the float32 estimate (2^24, where (float)i stops being exact)
   __device__ __forceinline__ void begin(int b, int first, int n) {
     af = afs.v[b];
     af32 = (float)af;
@@ -130,33 +132,30 @@ struct LoadResampled {
     thr = 0.5f - (1e-3f + 3e-7f * max_shift + max_step);
     c0 = first;
     n2 = n;
+    col_mask = (1u << lg_n2) - 1u;
   }
-  __device__ __forceinline__ void indices(int f, int idx, unsigned* i0, unsigned* i1) const {
+  // pair e of the natural series -> its place in the transposed layout (at most 2^24 pairs: 32-bit math)
+  __device__ __forceinline__ unsigned pair_index(unsigned e) const { return (e & col_mask) * (unsigned)n1 + (e >> lg_n2); }
+  __device__ __forceinline__ cf operator()(int f, int idx) const {
     const unsigned i = 2u * ((unsigned)idx * (unsigned)n2 + (unsigned)(c0 + f));
     const float fi = (float)i;                          // exact below 2^24
     const float g = (fi * (fi - fsize)) * af32;         // shift estimate
     const float tm = g + 12582912.f;                    // 1.5*2^23: rounds g to an integer (ties to even)
     const float r = tm - 12582912.f;
-    if (fabsf(g - r) < thr && i < (1u << 24)) {
-      *i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
-      *i1 = *i0 + 1;
-    } else {  // the reference's FP64 expression (kernels.cu:314-317)
-      *i0 = (unsigned)resample_index_II(af, size, i);
-      *i1 = (unsigned)resample_index_II(af, size, i + 1);
-    }
-  }
-  __device__ __forceinline__ size_t pair_addr(unsigned e) const {
-    return (size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2);
-  }
-  __device__ __forceinline__ cf operator()(int f, int idx) const {
-    unsigned i0, i1;
-    indices(f, idx, &i0, &i1);
-    if (((i0 & 1u) == 0) && i1 == i0 + 1) {  // both samples in one pair: one 8-byte load
-      float2 v = __ldg(&D[pair_addr(i0 >> 1)]);
-      return psfft::mk(v.x, v.y);
-    }
     const float* Df = reinterpret_cast<const float*>(D);
-    return psfft::mk(__ldg(&Df[2 * pair_addr(i0 >> 1) + (i0 & 1u)]), __ldg(&Df[2 * pair_addr(i1 >> 1) + (i1 & 1u)]));
+    if (fabsf(g - r) < thr && i < i_limit) {  // samples i0, i0 + 1
+      const unsigned i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
+      const unsigned e = i0 >> 1;
+      if ((i0 & 1u) == 0) {  // both samples in one pair: one 8-byte load
+        float2 v = __ldg(&D[pair_index(e)]);
+        return psfft::mk(v.x, v.y);
+      }
+      return psfft::mk(__ldg(&Df[2u * pair_index(e) + 1u]), __ldg(&Df[2u * pair_index(e + 1u)]));
+    }
+    // the reference's FP64 expression (kernels.cu:314-317), each sample on its own
+    const unsigned i0 = (unsigned)resample_index_II(af, size, i);
+    const unsigned i1 = (unsigned)resample_index_II(af, size, i + 1);
+    return psfft::mk(__ldg(&Df[2u * pair_index(i0 >> 1) + (i0 & 1u)]), __ldg(&Df[2u * pair_index(i1 >> 1) + (i1 & 1u)]));
   }
 };
 
