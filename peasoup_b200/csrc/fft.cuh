@@ -120,7 +120,7 @@ struct LoadResampled {
   double af;
   float af32, fsize, thr;
   int n2, c0;
-  unsigned col_mask;
+  unsigned col_mask, wrap;
   unsigned i_limit;  // host: sample indices below this take the float32 estimate (2^24, where (float)i stops being exact)
   __device__ __forceinline__ void begin(int b, int first, int n) {
     af = afs.v[b];
@@ -133,11 +133,15 @@ struct LoadResampled {
     c0 = first;
     n2 = n;
     col_mask = (1u << lg_n2) - 1u;
+    wrap = 1u - col_mask * (unsigned)n1;
   }
   // pair e of the natural series -> its place in the transposed layout (at most 2^24 pairs: 32-bit math)
   __device__ __forceinline__ unsigned pair_index(unsigned e) const { return (e & col_mask) * (unsigned)n1 + (e >> lg_n2); }
   __device__ __forceinline__ cf operator()(int f, int idx) const {
-    const unsigned i = 2u * ((unsigned)idx * (unsigned)n2 + (unsigned)(c0 + f));
+    return at(2u * ((unsigned)idx * (unsigned)n2 + (unsigned)(c0 + f)));
+  }
+  // samples map(i), map(i + 1) for an even sample index i
+  __device__ __forceinline__ cf at(unsigned i) const {
     const float fi = (float)i;                          // exact below 2^24
     const float g = (fi * (fi - fsize)) * af32;         // shift estimate
     const float tm = g + 12582912.f;                    // 1.5*2^23: rounds g to an integer (ties to even)
@@ -146,16 +150,34 @@ struct LoadResampled {
     if (fabsf(g - r) < thr && i < i_limit) {  // samples i0, i0 + 1
       const unsigned i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
       const unsigned e = i0 >> 1;
+      const unsigned p = pair_index(e);
       if ((i0 & 1u) == 0) {  // both samples in one pair: one 8-byte load
-        float2 v = __ldg(&D[pair_index(e)]);
+        float2 v = __ldg(&D[p]);
         return psfft::mk(v.x, v.y);
       }
-      return psfft::mk(__ldg(&Df[2u * pair_index(e) + 1u]), __ldg(&Df[2u * pair_index(e + 1u)]));
+      // pair e + 1 sits one column on (n1 pairs), or at the top of the next row after the last column
+      const unsigned p2 = p + (((e & col_mask) == col_mask) ? wrap : (unsigned)n1);
+      return psfft::mk(__ldg(&Df[2u * p + 1u]), __ldg(&Df[2u * p2]));
     }
     // the reference's FP64 expression (kernels.cu:314-317), each sample on its own
+    return exact(i);
+  }
+  __device__ __forceinline__ cf exact(unsigned i) const {
+    const float* Df = reinterpret_cast<const float*>(D);
     const unsigned i0 = (unsigned)resample_index_II(af, size, i);
     const unsigned i1 = (unsigned)resample_index_II(af, size, i + 1);
     return psfft::mk(__ldg(&Df[2u * pair_index(i0 >> 1) + (i0 & 1u)]), __ldg(&Df[2u * pair_index(i1 >> 1) + (i1 & 1u)]));
+  }
+
+  // The 16 operands of thread (f, u): rows u + a*G of the tile, a < 16 -- operator() with the sample
+  // index stepped by a constant instead of rebuilt from (f, idx) per element.
+  static constexpr bool kWholeColumn = true;
+  template <int G>
+  __device__ __forceinline__ void load_column(int f, int u, cf* v) const {
+    const unsigned ibase = 2u * ((unsigned)u * (unsigned)n2 + (unsigned)(c0 + f));
+    const unsigned di = 2u * (unsigned)G * (unsigned)n2;
+#pragma unroll
+    for (int a = 0; a < 16; a++) v[a] = at(ibase + (unsigned)a * di);
   }
 };
 
@@ -282,11 +304,20 @@ struct StoreNatural {  // out[k1 + n1*k2]
 // One work item = F transforms of one batch item.  The 16 operands of every thread for the NEXT
 // work item are loaded into registers between phase B and phase C of the current one (phase C
 // is the light radix-R3 stage), so their latency overlaps phase C and the stores.
+template <class L, class = void>
+struct loads_whole_column { static constexpr bool value = false; };
+template <class L>
+struct loads_whole_column<L, decltype((void)L::kWholeColumn)> { static constexpr bool value = true; };
+
 template <class C, class Loader>
 __device__ __forceinline__ void load_operands(const Loader& ld, cf* v) {
   const int t = threadIdx.x, f = t % C::F, u = t / C::F;
+  if constexpr (loads_whole_column<Loader>::value) {
+    ld.template load_column<C::G>(f, u, v);
+  } else {
 #pragma unroll
-  for (int a = 0; a < 16; a++) v[a] = ld(f, a * C::G + u);
+    for (int a = 0; a < 16; a++) v[a] = ld(f, a * C::G + u);
+  }
 }
 
 // grid-stride over (batch item, tile); items are independent transforms with their own Yt slice
