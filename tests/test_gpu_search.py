@@ -395,12 +395,14 @@ def test_harmonic_peaks_stage_bit_exact_vs_oracle(lib, oracle, size, nbatch, pad
     s.close()
 
 
-@pytest.mark.parametrize("size,acc_hi,a_inj", [(1 << 23, 50.0, 31.4), (1 << 24, 500.0, 312.5)])
+@pytest.mark.parametrize("size,acc_hi,a_inj", [(1 << 23, 50.0, 31.4), (1 << 24, 500.0, 312.5), (1 << 25, 500.0, 312.5)])
 def test_survey_sizes_vs_reference_cuda_build(lib, oracle, ref, size, acc_hi, a_inj, tmp_path):
     """BASELINE.json configs[3] and [4] shapes (2^23 samples, +-50 m/s^2; 2^24 samples, +-500 m/s^2)
     on one DM trial with the FULL acceleration lists of those configurations (101 and 201 trials):
     identical candidates to the unmodified reference build.  At 2^24 samples and 500 m/s^2 the resampling shift reaches ~3700 samples and
-    crosses a rounding boundary far more often than in the other tests (FP64 fallback of the loader)."""
+    crosses a rounding boundary far more often than in the other tests (FP64 fallback of the loader).
+    2^25 samples is the largest transform the engine takes: sample indices from 2^24 up are not exact
+    in float32 and always take the loader's FP64 expression."""
     tsamp = 64e-6
     nsamps = size + 4096
     trials = make_trials(1, nsamps, size, tsamp=tsamp, a_inj=a_inj, amp=3.0, seed=size % 1000)
