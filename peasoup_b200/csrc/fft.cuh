@@ -121,12 +121,11 @@ struct LoadResampled {
   float af32, fsize, thr;
   int n2, c0;
   unsigned col_mask, wrap;
-  unsigned i_limit;  // host: sample indices below this take the float32 estimate (2^24, where (float)i stops being exact)
   __device__ __forceinline__ void begin(int b, int first, int n) {
     af = afs.v[b];
     af32 = (float)af;
     fsize = (float)size;
-    // float32 evaluation error of the shift: fi and fi - N are exact, so three roundings (the
+    // float32 evaluation error of the shift: fi and fi - N are exact (even integers up to 2^25), so three roundings (the
     // product, af32 = float(af), the final product) give <= 1.8e-7 |shift| -- 3e-7 with margin.  A
     // shift estimate this far from a half-integer fixes the rounding of both samples of a pair.
     thr = 0.5f - (1e-3f + 3e-7f * max_shift + max_step);
@@ -142,12 +141,12 @@ struct LoadResampled {
   }
   // samples map(i), map(i + 1) for an even sample index i
   __device__ __forceinline__ cf at(unsigned i) const {
-    const float fi = (float)i;                          // exact below 2^24
+    const float fi = (float)i;                          // exact: i is even and below 2^25
     const float g = (fi * (fi - fsize)) * af32;         // shift estimate
     const float tm = g + 12582912.f;                    // 1.5*2^23: rounds g to an integer (ties to even)
     const float r = tm - 12582912.f;
     const float* Df = reinterpret_cast<const float*>(D);
-    if (fabsf(g - r) < thr && i < i_limit) {  // samples i0, i0 + 1
+    if (fabsf(g - r) < thr) {  // samples i0, i0 + 1
       const unsigned i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
       const unsigned e = i0 >> 1;
       const unsigned p = pair_index(e);

@@ -716,7 +716,6 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     ld.lg_n2 = s->lg_n2;
     for (int b = 0; b < nb; b++) ld.afs.v[b] = accel_fact(h_acc[j + b], s->prm.tsamp);
     ld.size = (double)size;
-    ld.i_limit = 1u << 24;
     {
       double amax = 0;
       for (int b = 0; b < nb; b++) amax = std::max(amax, fabs(ld.afs.v[b]));

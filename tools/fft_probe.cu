@@ -151,7 +151,7 @@ int main() {
     ld.D = reinterpret_cast<const float2*>(D);
     double af = ((30.0f * 64e-6f) / (2 * 299792458.0));
     for (int b = 0; b < 8; b++) ld.afs.v[b] = af * (b + 1) / 2;
-    ld.size = 2.0 * M; ld.n1 = n1; ld.lg_n2 = 11; ld.i_limit = 1u << 24;
+    ld.size = 2.0 * M; ld.n1 = n1; ld.lg_n2 = 11;
     ld.max_shift = (float)(af * 4 * 0.25 * ld.size * ld.size); ld.max_step = (float)(af * 4 * ld.size);
     run1<0>("full", ld, Yt, t, n1, n2, nbatch);
     run1<1>("noload", ld, Yt, t, n1, n2, nbatch);

@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(
 from synth import make_trials
 torch.cuda.set_device(0)
 for lg, amax, nacc, nfolds in ((20, 50.0, 101, 4), (21, 50.0, 101, 4), (22, 50.0, 101, 4), (23, 50.0, 101, 4), (23, 500.0, 201, 4),
-                               (23, 50.0, 101, 5), (23, 50.0, 101, 3), (24, 500.0, 201, 4)):
+                               (23, 50.0, 101, 5), (23, 50.0, 101, 3), (24, 500.0, 201, 4), (25, 500.0, 201, 4)):
     size, tsamp = 1 << lg, 64e-6
     trials = make_trials(1, size + 4096, size, tsamp=tsamp, a_inj=amax * 0.6, amp=3.0, seed=lg)
     accs = np.linspace(-amax, amax, nacc).astype(np.float32)
