@@ -338,12 +338,13 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, Ff
     C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
     __syncthreads();
     C::phaseB(threadIdx.x, smem, t.W4096, st);
-    __syncthreads();
+    // (issued before the barrier: the loads are in flight while the CTA waits for its slowest warp)
     const int next = work + gridDim.x;
     if (next < nwork) {
       ld.begin(next / ntiles, (next % ntiles) * C::F, n2);
       load_operands<C>(ld, v);
     }
+    __syncthreads();
     C::phaseC(threadIdx.x, smem, st);
   }
 }
