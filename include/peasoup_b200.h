@@ -187,6 +187,15 @@ int ps_search_harmonic_peaks(ps_search* s, const float* d_spectra, size_t stride
 /* Diagnostics for stage-by-stage parity tests: device pointers owned by the handle. */
 const float* ps_search_whitened_series(ps_search* s);   /* size floats */
 const float* ps_search_last_spectrum(ps_search* s);     /* size/2+1 floats (last accel trial) */
+/* Index map of the resampling gather that ps_search_accel_batch runs (TimeDomainResampler::resampleII,
+ * resampler.hpp:26-31 -> resample_kernelII / getAcceleratedIndexII, kernels.cu:314-317,335-346): the
+ * search path's own loader (fft.cuh LoadResampled: float32 shift estimate, FP64 expression near a
+ * rounding boundary) is executed over a series whose sample i holds the integer i, so d_idx[i]
+ * (DEVICE, size uint32) is the index that loader reads for output sample i at acceleration `acc`.
+ * *h_exact_pairs (optional) receives how many sample pairs evaluated the FP64 expression instead of
+ * the float32 estimate.  Diagnostics: allocates a scratch series and synchronises. */
+int ps_search_resample_index_map(ps_search* s, float acc, uint32_t* d_idx, unsigned* h_exact_pairs,
+                                 void* stream);
 /* kernel launch counter (all ps_* kernels launched by this process; for bench.py) */
 unsigned long long ps_launch_count(void);
 /* host<->device traffic issued by the pipeline driver: add to / read the process-wide counters */

@@ -68,7 +68,7 @@ SYMBOLS = [
     "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
     "ps_search_accel_batch", "ps_search_reset_peaks", "ps_search_fetch_peaks", "ps_search_peaks_needed",
     "ps_search_reserve_peaks",
-    "ps_search_harmonic_peaks", "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
+    "ps_search_harmonic_peaks", "ps_search_resample_index_map", "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
     "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
     "ps_pipeline_run", "ps_pipeline_close", "ps_dedisp_generate_dm_list", "ps_dedisp_max_delay",
     "ps_dedisperse", "ps_search_filterbank", "ps_fold_timeseries", "ps_fold_optimiser_create",
@@ -120,6 +120,7 @@ def load() -> C.CDLL:
         "ps_search_peaks_needed": [vp], "ps_search_reserve_peaks": [vp, u],
         "ps_search_harmonic_peaks": [vp, vp, sz, i, i, vp],
         "ps_search_whitened_series": [vp], "ps_search_last_spectrum": [vp],
+        "ps_search_resample_index_map": [vp, f, vp, C.POINTER(u), vp],
         "ps_pipeline_search": [C.POINTER(PipelineParams), vp, vp, i, i, vp, i, vp, vp, i, i, i, vp, C.c_long,
                                C.POINTER(C.c_ulonglong)],
         "ps_pipeline_open": [C.POINTER(PipelineParams), vp, vp, i, i, i, C.POINTER(vp)],

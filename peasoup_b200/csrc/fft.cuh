@@ -265,7 +265,9 @@ struct StorePass1 {
     for (int j = 0; j < R; j++) {
       cf o = psfft::cmul(v[j], pw[j]);
       const unsigned k = (unsigned)(k0 + stride * j);
-      out[(size_t)(k & ~twm) * n2 + (k & twm)] = make_float2(o.x, o.y);
+      // streaming store: the inter-pass data is read once, much later -- it should not displace the
+      // whitened series (re-read by every acceleration trial) from the L2
+      __stcs(&out[(size_t)(k & ~twm) * n2 + (k & twm)], make_float2(o.x, o.y));
     }
   }
 };
@@ -330,10 +332,13 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, Ff
   int work = blockIdx.x;
   if (work >= nwork) return;
   cf v[16];
-  ld.begin(work / ntiles, (work % ntiles) * C::F, n2);
+  // work items are ordered tile-major (all batch items of a tile, then the next tile): the CTAs
+  // running at any moment read the same few columns of the shared input, whatever the batch size,
+  // so the input needs no L2 residency across batch items
+  ld.begin(work % nbatch, (work / nbatch) * C::F, n2);
   load_operands<C>(ld, v);
   for (; work < nwork; work += gridDim.x) {
-    const int b = work / ntiles, tile = work - b * ntiles;
+    const int tile = work / nbatch, b = work - tile * nbatch;
     StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F, n2, tw2};
     C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
     __syncthreads();
@@ -341,7 +346,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, Ff
     // (issued before the barrier: the loads are in flight while the CTA waits for its slowest warp)
     const int next = work + gridDim.x;
     if (next < nwork) {
-      ld.begin(next / ntiles, (next % ntiles) * C::F, n2);
+      ld.begin(next % nbatch, (next / nbatch) * C::F, n2);
       load_operands<C>(ld, v);
     }
     __syncthreads();
@@ -567,13 +572,19 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_tma_kernel(const cf* Yt, con
 
 // ------------------------------------------------------------------ host-side launchers
 // opt in to > 48 KB dynamic shared memory once per (kernel instantiation, device); `done` must be
-// a static of the CALLING template (one per kernel), not of a helper keyed on the pointer type
+// a static of the CALLING template (one per kernel), not of a helper keyed on the pointer type.
+// Worker threads of different devices call this concurrently: the flag is atomic, and a thread that
+// finds it clear sets the attribute itself (setting it twice is harmless, skipping it is not).
+struct SmemOptIn {
+  std::atomic<bool> set{false};
+};
 template <class K>
-inline int configure_smem(K kernel, size_t bytes, int device, bool* done) {
-  if (!done[device & 63]) {
+inline int configure_smem(K kernel, size_t bytes, int device, SmemOptIn* done) {
+  SmemOptIn& d = done[device & 63];
+  if (!d.set.load(std::memory_order_acquire)) {
     PS_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes),
             "cudaFuncSetAttribute");
-    done[device & 63] = true;
+    d.set.store(true, std::memory_order_release);
   }
   return PS_OK;
 }
@@ -584,7 +595,7 @@ template <int R3, bool INV, class Loader>
 inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass1_kernel<R3, INV, Loader>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
@@ -597,7 +608,7 @@ template <int R3, bool INV, class Storer>
 inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t st, int nbatch, int reverse) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass2_kernel<R3, INV, Storer>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;  // exchange buffers + TMA staging tile
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
@@ -635,7 +646,7 @@ template <int R3, bool INV, class Loader>
 inline int launch_pass1_tma_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass1_tma_kernel<R3, INV, Loader>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
@@ -647,7 +658,7 @@ template <int R3, bool INV>
 inline int launch_pass2_tma_r(const ps_fft_plan_t* p, cudaStream_t st, int nbatch) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass2_tma_kernel<R3, INV>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;

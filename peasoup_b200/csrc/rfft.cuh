@@ -267,7 +267,7 @@ inline int launch_rfft_pass1_r(const ps_fft_plan_t* p, const RfftGeom& g, const 
                                int nbatch) {
   using C = psfft::CtaFft<R3, false>;
   auto k = rfft_pass1_kernel<R3>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   int rc = configure_smem(k, C::SMEM_BYTES, p->device, done);
   if (rc) return rc;
   k<<<fft_grid(g.C / C::F * nbatch), C::THREADS, C::SMEM_BYTES, st>>>(ld, Yr, g, p->W4096, p->TC, p->TD, nbatch);
@@ -280,7 +280,7 @@ inline int launch_rfft_pass2_r(const ps_fft_plan_t* p, const RfftGeom& g, const 
                                const float* stats, float fsize, cudaStream_t st, int nbatch) {
   using C = psfft::CtaFft<R3, false>;
   auto k = rfft_pass2_kernel<R3>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS + sizeof(cf) * g.L2;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;

@@ -295,6 +295,26 @@ __global__ void __launch_bounds__(256) untranspose_pairs_kernel(const float2* __
     out[e] = D[(size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2)];
 }
 
+// diagnostics (ps_search_resample_index_map): a series whose sample i is the bit pattern of i, in the
+// transposed pair layout, and the search path's loader run over all of its pairs
+__global__ void __launch_bounds__(256) ramp_pairs_kernel(float2* __restrict__ D, unsigned M, int n1, int lg_n2) {
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < M; e += gridDim.x * blockDim.x)
+    D[(size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2)] = make_float2(__uint_as_float(2u * e), __uint_as_float(2u * e + 1u));
+}
+__global__ void __launch_bounds__(256) loader_dump_kernel(LoadResampled ld, float2* __restrict__ out, unsigned M, int n2,
+                                                          unsigned* __restrict__ exact) {
+  ld.begin(0, 0, n2);
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < M; e += gridDim.x * blockDim.x) {
+    const cf v = ld.at(2u * e);
+    out[e] = make_float2(v.x, v.y);
+    // the test at() applies: count the pairs that went through the FP64 expression
+    const float fi = (float)(2u * e);
+    const float g = (fi * (fi - ld.fsize)) * ld.af32;
+    const float r = (g + 12582912.f) - 12582912.f;
+    if (!(fabsf(g - r) < ld.thr)) atomicAdd(exact, 1u);
+  }
+}
+
 // mean of the first n u8 samples (GPU_mean on the converted floats, pipeline_multi.cu:161)
 __global__ void __launch_bounds__(256) u8_sum_kernel(const unsigned char* __restrict__ b, size_t n, unsigned long long* __restrict__ acc) {
   unsigned long long s = 0;
@@ -459,7 +479,7 @@ static Search* SS(ps_search* s) { return reinterpret_cast<Search*>(s); }
 template <int NF>
 static int launch_harmonic_smem_nf(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
   auto k = harmonic_peaks_smem_kernel<NF>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = sizeof(float) * hs_total(NF) * kHsBufs;
   int rc = configure_smem(k, smem, s->plan->device, done);
   if (rc) return rc;
@@ -635,7 +655,7 @@ static int launch_pass2_spec(Search* s, int nb, cudaStream_t st) {
   const ps_fft_plan_t* p = s->plan;
   using C = psfft::CtaFft<8, false>;
   auto k = fft_pass2_spec_kernel<8>;
-  static bool done[64] = {};
+  static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
@@ -702,7 +722,11 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   static const bool env_tma = getenv("PS_TMA") ? atoi(getenv("PS_TMA")) != 0 : false;
   // profiling aid (tools/time_chain.py): leave kernels out of the chain to time the others;
   // 1 = pass 1, 2 = pass 2, 4 = spectrum, 8 = harmonic sums + peaks.  Results are garbage when set.
+#ifdef PS_PROFILING  // profiling builds only (make EXTRA=-DPS_PROFILING): the shipped library has no such switch
   static const int env_skip = getenv("PS_SKIP") ? atoi(getenv("PS_SKIP")) : 0;
+#else
+  constexpr int env_skip = 0;
+#endif
   static const int env_rev = getenv("PS_REVERSE") ? atoi(getenv("PS_REVERSE")) : 1;
   // balanced launches: 101 trials at up to 16 per launch run as 15+15+15+14+14+14+14, not 6x16+5
   int launches_left = (n_acc + env_batch - 1) / env_batch;
@@ -821,5 +845,44 @@ const float* ps_search_whitened_series(ps_search* hs) {
   return s->d_tim_nat;
 }
 const float* ps_search_last_spectrum(ps_search* s) { return s ? SS(s)->last_spectrum : nullptr; }
+
+// Index map of the PRODUCT resampling gather (diagnostics): the loader of ps_search_accel_batch is
+// run over a series whose sample i holds the 32-bit pattern of i, so d_idx[i] = map(i).
+int ps_search_resample_index_map(ps_search* hs, float acc, uint32_t* d_idx, unsigned* h_exact_pairs, void* stream) {
+  Search* s = SS(hs);
+  if (!s || !d_idx) return invalid("ps_search_resample_index_map: null argument");
+  if (s->fused) return invalid("ps_search_resample_index_map: not available with PS_FUSED");
+  cudaStream_t st = S(stream);
+  const ps_fft_plan_t* p = s->plan;
+  const unsigned size = s->prm.size;
+  float2* ramp = nullptr;
+  unsigned* d_cnt = nullptr;
+  PS_CUDA(cudaMalloc(&ramp, sizeof(float) * (size_t)size), "Error from device_malloc");
+  if (cudaMalloc(&d_cnt, sizeof(unsigned)) != cudaSuccess) {
+    cudaFree(ramp);
+    return cuda_fail(cudaGetLastError(), "Error from device_malloc");
+  }
+  cudaMemsetAsync(d_cnt, 0, sizeof(unsigned), st);
+  ramp_pairs_kernel<<<ew_grid(p->M, 256, 2), 256, 0, st>>>(ramp, p->M, s->col_len, s->lg_n2);
+  g_launches.fetch_add(1);
+  LoadResampled ld;  // set up exactly as ps_search_accel_batch does for a one-trial batch
+  ld.D = ramp;
+  ld.n1 = s->col_len;
+  ld.lg_n2 = s->lg_n2;
+  ld.afs.v[0] = accel_fact(acc, s->prm.tsamp);
+  ld.size = (double)size;
+  ld.max_shift = (float)(fabs(ld.afs.v[0]) * 0.25 * (double)size * (double)size * 1.001);
+  ld.max_step = (float)(fabs(ld.afs.v[0]) * (double)size * 1.001);
+  loader_dump_kernel<<<ew_grid(p->M, 256, 2), 256, 0, st>>>(ld, reinterpret_cast<float2*>(d_idx), p->M, p->n2, d_cnt);
+  g_launches.fetch_add(1);
+  unsigned cnt = 0;
+  cudaError_t e = cudaMemcpyAsync(&cnt, d_cnt, sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(ramp);
+  cudaFree(d_cnt);
+  if (e != cudaSuccess) return cuda_fail(e, "ps_search_resample_index_map");
+  if (h_exact_pairs) *h_exact_pairs = cnt;
+  return PS_OK;
+}
 
 }  // extern "C"

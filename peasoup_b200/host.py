@@ -90,6 +90,13 @@ class Search:
         n = check(load().ps_search_fetch_peaks(self._h, ptr(self._peaks), len(self._peaks), stream_ptr(stream)))
         return self._peaks[:n].copy()
 
+    def resample_index_map(self, acc, d_idx, stream=None) -> int:
+        """Index map of the search path's resampling gather into d_idx (uint32, size); returns the
+        number of sample pairs that took the FP64 path."""
+        n = C.c_uint()
+        check(load().ps_search_resample_index_map(self._h, float(acc), ptr(d_idx), C.byref(n), stream_ptr(stream)))
+        return n.value
+
     def whitened_series_ptr(self) -> int:
         return load().ps_search_whitened_series(self._h)
 
