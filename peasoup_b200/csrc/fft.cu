@@ -60,28 +60,6 @@ static std::vector<cf> roots(unsigned count, unsigned step, unsigned period) {
   return v;
 }
 
-// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency)
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static bool encode_3d(CUtensorMap* tm, void* base, cuuint64_t d0_floats, cuuint64_t d1, cuuint64_t d2, cuuint64_t pitch1_bytes,
-                      cuuint64_t pitch2_bytes, cuuint32_t box0_floats, cuuint32_t box1) {
-  void* fn = nullptr;
-  cudaDriverEntryPointQueryResult q;
-  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) {
-    cudaGetLastError();
-    return false;
-  }
-  cuuint64_t dims[3] = {d0_floats, d1, d2};
-  cuuint64_t strides[2] = {pitch1_bytes, pitch2_bytes};
-  cuuint32_t box[3] = {box0_floats, box1, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = ((EncodeTiledFn)fn)(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS;
-}
-
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch) {
   if (max_batch < 1 || max_batch > kMaxBatch) return invalid("plan_create: bad batch");
   if (n < (1u << 17) || n > (1u << 25) || (n & (n - 1)))
@@ -121,17 +99,6 @@ int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch) {
     cudaFree(p->W4096); cudaFree(p->TA); cudaFree(p->TB); cudaFree(p->Yt); cudaFree(p->Z); cudaFree(p->TC); cudaFree(p->TD);
     delete p;
     return cuda_fail(e, "Error from device_malloc");
-  }
-  {
-    // descriptors of the search path's asynchronous tile stores (three-stage transforms only)
-    const int F1 = 32 / p->r1, F2 = 32 / p->r2, tw = F2;
-    const cuuint64_t Mb = (cuuint64_t)p->M * sizeof(cf);
-    const int rows1 = p->n1 / tw;
-    p->has_tma = p->r1 > 1 && p->r2 > 1 &&
-                 encode_3d(&p->tm_yt, p->Yt, 2ull * p->n2 * tw, rows1, max_batch, (cuuint64_t)p->n2 * tw * sizeof(cf), Mb, 2 * F1 * tw,
-                           rows1 < 256 ? rows1 : 256) &&
-                 encode_3d(&p->tm_z, p->Z, 2ull * p->n1, p->n2, max_batch, (cuuint64_t)p->n1 * sizeof(cf), Mb, 2 * F2,
-                           p->n2 < 256 ? p->n2 : 256);
   }
   *out = p;
   return PS_OK;

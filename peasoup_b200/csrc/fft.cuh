@@ -38,10 +38,6 @@ struct ps_fft_plan_t {
   cf* Z;   // max_batch x M complex: packed-complex spectrum before the real post-process
   cf* TC;  // exp(-i pi 4096 q / M), q <= M/4096   (real-FFT split twiddle W_N^k, N = 2M)
   cf* TD;  // exp(-i pi q / M), q < 4096
-  // TMA descriptors for the asynchronous tile stores of the search path (fft_pass*_tma_kernel)
-  bool has_tma;
-  CUtensorMap tm_yt;  // tiled inter-pass buffer Yt[k1/tw][j2][k1%tw] as {2*n2*tw floats, n1/tw rows, batch}
-  CUtensorMap tm_z;   // natural packed spectrum Z[k1 + n1*k2] as {2*n1 floats, n2 rows, batch}
   FftTables tables() const { return FftTables{W4096, TA, TB}; }
 };
 
@@ -433,143 +429,6 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
   }
 }
 
-// ---- TMA tile stores: results are staged in shared memory (the E1 exchange region, idle after
-// phase B) and written back by one thread with cp.async.bulk.tensor, overlapping the next tile.
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* tm, const void* smem_src, int c0, int c1, int c2) {
-  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tm), "r"(c0), "r"(c1),
-               "r"(c2), "r"(smem_u32(smem_src))
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-
-// Storer writing into the shared-memory staging tile; pass 1 also applies the inter-pass twiddle.
-// Layout = the TMA box: pass 1 [k1/tw][f][k1%tw], pass 2 [k2][f].
-template <bool INV, bool PASS1>
-struct StageStore {
-  cf* stage;
-  FftTables t;
-  int c0;  // first column of the tile (pass 1: twiddle index)
-  int tw;  // pass 1: rows per pass-2 tile
-  template <int R>
-  __device__ __forceinline__ void store(int f, int k0, int stride, const cf* v) const {
-    constexpr int F = 0;
-    (void)F;
-    if (PASS1) {
-      const unsigned j2 = (unsigned)(c0 + f);
-      const cf base = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k0));
-      cf pw[R > 1 ? R : 2];
-      psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride)));
-      const unsigned twm = (unsigned)tw - 1u;
-#pragma unroll
-      for (int j = 0; j < R; j++) {
-        const unsigned k = (unsigned)(k0 + stride * j);
-        stage[((k & ~twm) * nf) + f * tw + (k & twm)] = psfft::cmul(v[j], pw[j]);
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < R; j++) stage[(k0 + stride * j) * nf + f] = v[j];
-    }
-  }
-  int nf;  // FFTs per tile (C::F)
-};
-
-template <int R3, bool INV, class Loader>
-__global__ void __launch_bounds__(512, 1) fft_pass1_tma_kernel(Loader ld, const __grid_constant__ CUtensorMap tm, FftTables t, int n1,
-                                                               int n2, int nbatch, int tw2) {
-  using C = psfft::CtaFft<R3, INV>;
-  extern __shared__ __align__(128) float smem[];
-  const int ntiles = n2 / C::F;
-  const int nwork = ntiles * nbatch;
-  int work = blockIdx.x;
-  if (work >= nwork) return;
-  cf* stage = reinterpret_cast<cf*>(smem);  // E1 region
-  const int rows = n1 / tw2, box_rows = rows < 256 ? rows : 256;
-  cf v[16];
-  ld.begin(work / ntiles, (work % ntiles) * C::F, n2);
-  load_operands<C>(ld, v);
-  for (; work < nwork; work += gridDim.x) {
-    const int b = work / ntiles, tile = work - b * ntiles;
-    StageStore<INV, true> st{stage, t, tile * C::F, tw2, C::F};
-    C::phaseA_compute(threadIdx.x, t.W4096, v);
-    if (threadIdx.x == 0) bulk_wait_read();  // previous tile's store has finished reading E1
-    __syncthreads();
-    C::phaseA_write(threadIdx.x, smem, v);
-    __syncthreads();
-    C::phaseB(threadIdx.x, smem, t.W4096, st);
-    __syncthreads();
-    const int next = work + gridDim.x;
-    if (next < nwork) {
-      ld.begin(next / ntiles, (next % ntiles) * C::F, n2);
-      load_operands<C>(ld, v);
-    }
-    C::phaseC(threadIdx.x, smem, st);
-    fence_proxy_async();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      for (int r = 0; r < rows; r += box_rows)
-        tma_store_3d(&tm, stage + (size_t)r * C::F * tw2, 2 * tile * C::F * tw2, r, b);
-      bulk_commit();
-    }
-  }
-  if (threadIdx.x == 0) bulk_wait_read();
-}
-
-template <int R3, bool INV>
-__global__ void __launch_bounds__(512, 1) fft_pass2_tma_kernel(const cf* Yt, const __grid_constant__ CUtensorMap tm, FftTables t,
-                                                               int n1, int n2, int nbatch) {
-  using C = psfft::CtaFft<R3, INV>;
-  extern __shared__ __align__(128) float smem[];
-  __shared__ __align__(8) unsigned long long bar;
-  const int ntiles = n1 / C::F;
-  const int nwork = ntiles * nbatch;
-  const size_t tile_elems = (size_t)n2 * C::F;
-  constexpr unsigned kTileBytes = sizeof(cf) * 16 * C::THREADS;
-  cf* in_stage = reinterpret_cast<cf*>(smem + C::SMEM_WORDS);
-  cf* out_stage = reinterpret_cast<cf*>(smem);  // E1 region
-  int work = blockIdx.x;
-  if (work >= nwork) return;
-  if (threadIdx.x == 0) {
-    mbar_init(&bar, 1);
-    fence_proxy_async();
-    mbar_expect_tx(&bar, kTileBytes);
-    bulk_g2s(in_stage, Yt + (size_t)work * tile_elems, kTileBytes, &bar);
-  }
-  __syncthreads();
-  unsigned parity = 0;
-  const int box_rows = n2 < 256 ? n2 : 256;
-  for (; work < nwork; work += gridDim.x) {
-    const int b = work / ntiles, tile = work - b * ntiles;
-    StageStore<INV, false> st{out_stage, t, 0, 0, C::F};
-    mbar_wait(&bar, parity);
-    parity ^= 1u;
-    cf v[16];
-#pragma unroll
-    for (int a = 0; a < 16; a++) v[a] = in_stage[a * C::THREADS + threadIdx.x];
-    C::phaseA_compute(threadIdx.x, t.W4096, v);
-    if (threadIdx.x == 0) bulk_wait_read();  // previous tile's store has finished reading E1
-    __syncthreads();                          // ... and every thread has taken its operands
-    const int next = work + gridDim.x;
-    if (threadIdx.x == 0 && next < nwork) {
-      fence_proxy_async();
-      mbar_expect_tx(&bar, kTileBytes);
-      bulk_g2s(in_stage, Yt + (size_t)next * tile_elems, kTileBytes, &bar);
-    }
-    C::phaseA_write(threadIdx.x, smem, v);
-    __syncthreads();
-    C::phaseB(threadIdx.x, smem, t.W4096, st);
-    __syncthreads();
-    C::phaseC(threadIdx.x, smem, st);
-    fence_proxy_async();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      for (int r = 0; r < n2; r += box_rows) tma_store_3d(&tm, out_stage + (size_t)r * C::F, 2 * tile * C::F, r, b);
-      bulk_commit();
-    }
-  }
-  if (threadIdx.x == 0) bulk_wait_read();
-}
-
 // ------------------------------------------------------------------ host-side launchers
 // opt in to > 48 KB dynamic shared memory once per (kernel instantiation, device); `done` must be
 // a static of the CALLING template (one per kernel), not of a helper keyed on the pointer type.
@@ -639,52 +498,6 @@ inline int launch_pass2(const ps_fft_plan_t* p, const Storer& stor, cudaStream_t
 #define PS_CALL2(R) launch_pass2_r<R, INV, Storer>(p, stor, st, nbatch, reverse)
   PS_DISPATCH_R(p->r2, PS_CALL2)
 #undef PS_CALL2
-}
-
-// TMA-store variants (search path; require p->has_tma and R3 > 1)
-template <int R3, bool INV, class Loader>
-inline int launch_pass1_tma_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch) {
-  using C = psfft::CtaFft<R3, INV>;
-  auto k = fft_pass1_tma_kernel<R3, INV, Loader>;
-  static SmemOptIn done[64];
-  const size_t smem = C::SMEM_BYTES;
-  int rc = configure_smem(k, smem, p->device, done);
-  if (rc) return rc;
-  k<<<fft_grid(p->n2 / C::F * nbatch), C::THREADS, smem, st>>>(ld, p->tm_yt, p->tables(), p->n1, p->n2, nbatch, 32 / p->r2);
-  PS_LAUNCHED("fft_pass1_tma_kernel");
-  return PS_OK;
-}
-template <int R3, bool INV>
-inline int launch_pass2_tma_r(const ps_fft_plan_t* p, cudaStream_t st, int nbatch) {
-  using C = psfft::CtaFft<R3, INV>;
-  auto k = fft_pass2_tma_kernel<R3, INV>;
-  static SmemOptIn done[64];
-  const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;
-  int rc = configure_smem(k, smem, p->device, done);
-  if (rc) return rc;
-  k<<<fft_grid(p->n1 / C::F * nbatch), C::THREADS, smem, st>>>(p->Yt, p->tm_z, p->tables(), p->n1, p->n2, nbatch);
-  PS_LAUNCHED("fft_pass2_tma_kernel");
-  return PS_OK;
-}
-template <bool INV, class Loader>
-inline int launch_pass1_tma(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch) {
-  switch (p->r1) {
-    case 2: return launch_pass1_tma_r<2, INV, Loader>(p, ld, st, nbatch);
-    case 4: return launch_pass1_tma_r<4, INV, Loader>(p, ld, st, nbatch);
-    case 8: return launch_pass1_tma_r<8, INV, Loader>(p, ld, st, nbatch);
-    case 16: return launch_pass1_tma_r<16, INV, Loader>(p, ld, st, nbatch);
-    default: return invalid("TMA pass 1 needs a three-stage transform");
-  }
-}
-template <bool INV>
-inline int launch_pass2_tma(const ps_fft_plan_t* p, cudaStream_t st, int nbatch) {
-  switch (p->r2) {
-    case 2: return launch_pass2_tma_r<2, INV>(p, st, nbatch);
-    case 4: return launch_pass2_tma_r<4, INV>(p, st, nbatch);
-    case 8: return launch_pass2_tma_r<8, INV>(p, st, nbatch);
-    case 16: return launch_pass2_tma_r<16, INV>(p, st, nbatch);
-    default: return invalid("TMA pass 2 needs a three-stage transform");
-  }
 }
 
 // Z (M packed-complex bins in p->Z) -> X[0..M] (fft.cu)

@@ -15,13 +15,11 @@
 #include <cstdint>
 #include <cstdlib>
 #include <vector>
-#include "rfft.cuh"
+#include "fft.cuh"
 
 namespace ps {
 
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
-constexpr int kP2sGrid = 148;           // CTAs of the fused pass-2 + spectrum kernel (one per SM)
-constexpr int kP2sLag = 2 * kP2sGrid;   // positions between a tile and the spectrum item that reads it
 constexpr int kAccelBatch = 32;  // acceleration trials per launch: amortises kernel ramp-up/drain and the 148-SM wave tail (measured us/trial: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7)
 void plan_destroy(ps_fft_plan_t* p);
 
@@ -130,9 +128,6 @@ __global__ void __launch_bounds__(256) spectrum_kernel(const float2* __restrict_
   }
 }
 
-}  // namespace ps
-#include "pass2spec.cuh"
-namespace ps {
 
 struct PeakSink {
   ps_raw_peak* peaks;
@@ -415,9 +410,6 @@ struct Search {
   float* d_tim_nat = nullptr;  // natural-order copy, made on request (ps_search_whitened_series)
   int lg_n2 = 0;    // log2(pair columns) of the transposed whitened series
   int col_len = 0;  // pairs per column
-  bool fused = false;  // real-input two-kernel path (rfft.cuh) available for this size
-  RfftGeom geom;
-  cf* d_yr = nullptr;  // its tiled inter-pass buffer (kAccelBatch transforms)
   float2* d_X = nullptr;       // nbins complex
   float* d_pspec = nullptr;    // nbins
   float* d_median = nullptr;   // nbins
@@ -435,9 +427,6 @@ struct Search {
   LevelRanges ranges;
   LevelScales scales;
   float* d_pbatch = nullptr;   // kBatch spectra (stride pstride floats)
-  float2* d_ring = nullptr;    // pass2spec.cuh: ring of pass-2 tiles (packed spectrum rows), L2-resident
-  int* d_progress = nullptr;   // pass2spec.cuh: per-CTA progress counters
-  int ring_slots = 0;          // 0: the fused pass-2 + spectrum kernel is not used for this size
   size_t pstride = 0;
   const float* last_spectrum = nullptr;
   float bin_width_f = 0.f;   // float bin_width = 1.0/tobs   (pipeline_multi.cu:118-119)
@@ -449,7 +438,7 @@ static void free_search(Search* s) {
   plan_destroy(s->plan);
   cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
-  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch); cudaFree(s->d_ring); cudaFree(s->d_progress); cudaFree(s->d_yr);
+  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch);
   delete s;
 }
 
@@ -511,14 +500,6 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   s->nbins = size / 2 + 1;
   while ((1 << s->lg_n2) < s->plan->n2) s->lg_n2++;
   s->col_len = s->plan->n1;
-  // Experimental two-kernel real-input path (rfft.cuh): parity-green, but measured slower than the
-  // packed transform + spectrum_kernel at 2^23 (96 vs 68 us/trial: its 4096-point column pass and
-  // 16-byte spectrum stores cost more than the packed spectrum round trip saves) -> opt-in only.
-  s->fused = rfft_geometry(size, &s->geom) && getenv("PS_FUSED") && atoi(getenv("PS_FUSED")) == 1;
-  if (s->fused) {  // the whitened series is transposed for the fused path's columns instead
-    s->lg_n2 = s->geom.lgC;
-    s->col_len = s->geom.L1;
-  }
   float tobs = size * p->tsamp;            // pipeline_multi.cu:118
   float bin_width = 1.0 / tobs;            // :119
   s->bin_width_f = bin_width;
@@ -550,16 +531,6 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (e == cudaSuccess) e = cudaMalloc(&s->d_peaks, sizeof(ps_raw_peak) * (size_t)s->cap);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_count, sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * kAccelBatch);
-  // fused pass 2 + spectrum (pass2spec.cuh; 2048-point rows in 4-row tiles): parity-green, keeps the
-  // packed spectrum out of DRAM, but measured slower than the two kernels (31.5 vs 21.0 us/trial
-  // for this portion: one 512-thread CTA per SM exposes every L2 round trip of the spectrum part),
-  // so it is opt-in: PS_P2S=1
-  if (e == cudaSuccess && !s->fused && s->plan->r2 == 8 && s->plan->n1 >= 64 && getenv("PS_P2S") && atoi(getenv("PS_P2S")) == 1) {
-    s->ring_slots = 2 * kP2sLag + kP2sGrid + 28;  // >= 2 lag + grid + 16 (pass2spec.cuh)
-    e = cudaMalloc(&s->d_ring, sizeof(float2) * (size_t)s->ring_slots * 4 * s->plan->n2);
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_progress, sizeof(int) * kP2sGrid);
-  }
-  if (e == cudaSuccess && s->fused) e = cudaMalloc(&s->d_yr, sizeof(cf) * s->geom.ystride * kAccelBatch);
   if (e == cudaSuccess) e = cudaMemset(s->d_count, 0, sizeof(unsigned));
   if (e != cudaSuccess) {
     free_search(s);
@@ -650,23 +621,6 @@ static int launch_spectrum(Search* s, int nb, cudaStream_t st) {
   return PS_OK;
 }
 
-// pass 2 + spectrum in one persistent kernel (pass2spec.cuh)
-static int launch_pass2_spec(Search* s, int nb, cudaStream_t st) {
-  const ps_fft_plan_t* p = s->plan;
-  using C = psfft::CtaFft<8, false>;
-  auto k = fft_pass2_spec_kernel<8>;
-  static SmemOptIn done[64];
-  const size_t smem = C::SMEM_BYTES + sizeof(cf) * 16 * C::THREADS;
-  int rc = configure_smem(k, smem, p->device, done);
-  if (rc) return rc;
-  PS_CUDA(cudaMemsetAsync(s->d_progress, 0, sizeof(int) * kP2sGrid, st), "launch_pass2_spec");
-  SpecArgs sa{s->d_pbatch, s->pstride, s->d_stats, (float)s->prm.size, p->TC, p->TD,
-              make_float2((float)cos(M_PI / (double)p->M), (float)-sin(M_PI / (double)p->M))};
-  k<<<kP2sGrid, C::THREADS, smem, st>>>(p->Yt, s->d_ring, s->ring_slots, s->d_progress, p->tables(), p->n1, p->n2, nb, kP2sLag, sa, getenv("PS_DBG") ? atoi(getenv("PS_DBG")) : 0);
-  PS_LAUNCHED("fft_pass2_spec_kernel");
-  return PS_OK;
-}
-
 // harmonic sums + peaks of nb spectra (blockIdx.y = spectrum)
 static int launch_harmonic_peaks(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
   PeakSink sink{s->d_peaks, s->d_count, s->cap};
@@ -717,11 +671,6 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   unsigned size = s->prm.size;
   int rc;
   static const int env_batch = getenv("PS_BATCH") ? std::max(1, std::min(kAccelBatch, atoi(getenv("PS_BATCH")))) : kAccelBatch;
-  // TMA tensor-map tile stores (fft_pass*_tma_kernel) measured ~3 % slower than plain stores on
-  // this workload (the passes are issue-bound, not store-latency-bound): opt-in via PS_TMA=1
-  static const bool env_tma = getenv("PS_TMA") ? atoi(getenv("PS_TMA")) != 0 : false;
-  // profiling aid (tools/time_chain.py): leave kernels out of the chain to time the others;
-  // 1 = pass 1, 2 = pass 2, 4 = spectrum, 8 = harmonic sums + peaks.  Results are garbage when set.
 #ifdef PS_PROFILING  // profiling builds only (make EXTRA=-DPS_PROFILING): the shipped library has no such switch
   static const int env_skip = getenv("PS_SKIP") ? atoi(getenv("PS_SKIP")) : 0;
 #else
@@ -746,22 +695,11 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
       ld.max_shift = (float)(amax * 0.25 * (double)size * (double)size * 1.001);  // |i(i-N)| <= N^2/4
       ld.max_step = (float)(amax * (double)size * 1.001);                         // |d/di| <= N
     }
-    if (s->fused) {
-      if ((rc = launch_rfft_pass1(p, s->geom, ld, s->d_yr, st, nb))) return rc;
-      if ((rc = launch_rfft_pass2(p, s->geom, s->d_yr, s->d_pbatch, s->pstride, s->d_stats, (float)size, st, nb))) return rc;
-    } else if (p->has_tma && env_tma) {
-      if ((rc = launch_pass1_tma<false>(p, ld, st, nb))) return rc;
-      if ((rc = launch_pass2_tma<false>(p, st, nb))) return rc;
-      if ((rc = launch_spectrum(s, nb, st))) return rc;
-    } else {
-      if (!(env_skip & 1) && (rc = launch_pass1<false>(p, ld, st, nb))) return rc;
-      if (s->ring_slots && !(env_skip & 6)) {
-        if ((rc = launch_pass2_spec(s, nb, st))) return rc;
-      } else {
-        StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
-        if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb, env_rev))) return rc;
-        if (!(env_skip & 4) && (rc = launch_spectrum(s, nb, st))) return rc;
-      }
+    if (!(env_skip & 1) && (rc = launch_pass1<false>(p, ld, st, nb))) return rc;
+    {
+      StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
+      if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb, env_rev))) return rc;
+      if (!(env_skip & 4) && (rc = launch_spectrum(s, nb, st))) return rc;
     }
     if (env_skip & 8) continue;
     static const int env_hsmem = getenv("PS_HSMEM") ? atoi(getenv("PS_HSMEM")) : 1;
@@ -851,7 +789,6 @@ const float* ps_search_last_spectrum(ps_search* s) { return s ? SS(s)->last_spec
 int ps_search_resample_index_map(ps_search* hs, float acc, uint32_t* d_idx, unsigned* h_exact_pairs, void* stream) {
   Search* s = SS(hs);
   if (!s || !d_idx) return invalid("ps_search_resample_index_map: null argument");
-  if (s->fused) return invalid("ps_search_resample_index_map: not available with PS_FUSED");
   cudaStream_t st = S(stream);
   const ps_fft_plan_t* p = s->plan;
   const unsigned size = s->prm.size;

@@ -84,57 +84,6 @@ def test_whiten_and_spectrum_vs_oracle(lib, oracle, size, nsamps, zap):
     s.close()
 
 
-@pytest.mark.parametrize("size", [1 << 20, 1 << 21])
-def test_experimental_real_input_path_vs_oracle(lib, oracle, size, monkeypatch):
-    """PS_FUSED=1 selects the two-kernel real-input transform (rfft.cuh) when the handle is created."""
-    monkeypatch.setenv("PS_FUSED", "1")
-    tsamp = 64e-6
-    trial = make_trials(1, size, size, tsamp=tsamp, a_inj=20.0, amp=8.0)[0]
-    cfg = oracle.SearchConfig(size, tsamp)
-    s = pb.Search(make_search_params(size, size, tsamp))
-    s.whiten(torch.from_numpy(trial).cuda())
-    tim, wmean, wstd = oracle.whiten(trial, cfg)
-    for acc in (0.0, 20.0, -47.3):
-        s.reset_peaks()
-        s.accel_batch([acc])
-        p = dev_f32(s.last_spectrum_ptr(), cfg.nbins)
-        want = oracle.accel_spectrum(tim, acc, wmean, wstd, cfg)
-        assert np.abs(p - want).max() < 20 * SPEC_TOL and np.sqrt(((p - want) ** 2).mean()) < SPEC_TOL
-    s.close()
-
-
-@pytest.mark.parametrize("knob", ["PS_P2S"])
-def test_experimental_kernels_equal_the_default_path(lib, knob, monkeypatch):
-    """The opt-in experiment that keeps the packed transform (pass 2 + spectrum fused over an L2-resident
-    ring, pass2spec.cuh) runs the same arithmetic in a different schedule:
-    the spectra agree to a few ulp (the compiler contracts multiply-adds differently in the two
-    kernels) and the peak lists are the same apart from bins at the threshold.  2^23 samples: the
-    size PS_P2S supports."""
-    size, tsamp = 1 << 23, 64e-6
-    trial = torch.from_numpy(make_trials(1, size, size, tsamp=tsamp, a_inj=20.0, amp=6.0)[0]).cuda()
-    accs = np.array([0.0, 20.0, -47.3, 3.5, 11.0], np.float32)
-
-    def run():
-        s = pb.Search(make_search_params(size, size, tsamp, min_snr=7.0))
-        s.whiten(trial)
-        s.reset_peaks()
-        s.accel_batch(accs)
-        peaks = s.fetch_peaks()
-        spec = dev_f32(s.last_spectrum_ptr(), size // 2 + 1).copy()
-        s.close()
-        return peaks, spec
-
-    base_peaks, base_spec = run()
-    monkeypatch.setenv(knob, "1")
-    peaks, spec = run()
-    assert len(base_peaks) > 100
-    assert np.abs(spec - base_spec).max() < 1e-4
-    a = {(int(r["acc_idx"]), int(r["nh"]), int(r["bin"])): float(r["snr"]) for r in base_peaks}
-    b = {(int(r["acc_idx"]), int(r["nh"]), int(r["bin"])): float(r["snr"]) for r in peaks}
-    assert all(abs((a.get(k) or b.get(k)) - 7.0) < 1e-3 for k in set(a) ^ set(b))
-    assert max(abs(a[k] - b[k]) for k in set(a) & set(b)) < 1e-3
-
-
 @pytest.mark.parametrize("size", [1 << 17, 1 << 19, 1 << 20, 1 << 21, 1 << 22, 1 << 23, 1 << 24, 1 << 25])
 def test_product_resample_index_map_bit_exact(lib, oracle, size):
     """north_star: resampling index maps are bit-exact.  ps_search_resample_index_map runs the loader
