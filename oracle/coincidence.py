@@ -7,8 +7,13 @@ Follows src/coincidencer.cpp:122-214 (per-beam whitening and normalisation), coi
 (include/transforms/coincidencer.hpp:41-77).  The transforms are numpy's (any length, double,
 rounded to float32) standing in for cuFFT.
 
-Parity unpinned: the reference holds no golden output for this tool; the whitening stages it
-re-uses are the ones pinned by the golden candidate file (oracle.py).
+Pinned by the reference run here: match() against the unmodified coincidence_kernel of
+oracle/_ref on the same arrays (tests/test_gpu_coincidence.py::
+test_coincidencer_kernel_equals_reference_kernel, bit-exact including threshold ties and NaNs);
+every per-beam stage of whiten_beam() is one of the staged functions that tests/test_gpu_stages.py
+pins against the same reference build, and by the golden candidate file (oracle.py).  The reference
+holds no golden output for the program as a whole, so the file writers are checked against the
+reference's format only (coincidencer.hpp:41-77).
 """
 import numpy as np
 

@@ -23,6 +23,7 @@
 #include <transforms/peakfinder.hpp>
 #include <transforms/distiller.hpp>
 #include <transforms/harmonicfolder.hpp>
+#include <data_types/folded.hpp>
 #include <utils/exceptions.hpp>
 #include <utils/utils.hpp>
 #include <utils/stats.hpp>
@@ -34,6 +35,7 @@
 #define private public
 #include <transforms/dereddener.hpp>
 #undef private
+#include <transforms/folder.hpp>
 #include <string>
 #include <vector>
 
@@ -306,6 +308,44 @@ int ref_whiten(const RefSearchParams* p, unsigned char* h_trial, float* d_tim_ou
   *mean_out = mean;
   *std_out = std;
   if (bzap) delete bzap;
+  REF_CATCH
+}
+
+/* ---- rows f3 / f4 of SURVEY 8: folding, fold optimisation, coincidence matching -------------- */
+
+/* device_fold_timeseries (src/kernels.cu:634-651), launched the way TimeSeriesFolder::fold does
+ * (folder.hpp:48-61: max_blocks = nints, max_threads = nbins) */
+int ref_fold_timeseries(float* d_in, float* d_out, size_t nsamps, size_t nsubints, double period, double tsamp,
+                        int nbins) {
+  REF_TRY
+  device_fold_timeseries(d_in, d_out, nsamps, nsubints, period, tsamp, nbins, nsubints, nbins);
+  REF_CATCH
+}
+
+/* FoldOptimiser::optimise (folder.hpp:241-351) with the reference's own object on d_fold[nints][nbins] */
+int ref_fold_optimise(const float* d_fold, unsigned nbins, unsigned nints, double period, float tobs, float* opt_sn,
+                      double* opt_period, int* opt_width, int* opt_bin, float* h_opt_fold, float* h_opt_prof) {
+  REF_TRY
+  FoldedSubints<float> fold(nbins, nints);
+  Utils::d2dcpy(fold.get_data(), const_cast<float*>(d_fold), (size_t)nbins * nints);
+  fold.set_period(period);
+  fold.set_tobs(tobs);
+  FoldOptimiser opt(nbins, nints);
+  opt.optimise(fold);
+  *opt_sn = fold.get_opt_sn();
+  *opt_period = fold.get_opt_period();  /* NB: the getter narrows to float (folded.hpp:43) */
+  *opt_width = fold.get_opt_width();
+  *opt_bin = fold.get_opt_bin();
+  if (h_opt_fold) memcpy(h_opt_fold, &fold.opt_fold[0], sizeof(float) * nbins * nints);
+  if (h_opt_prof) memcpy(h_opt_prof, &fold.opt_prof[0], sizeof(float) * nbins);
+  REF_CATCH
+}
+
+/* device_coincidencer (src/kernels.cu:1073-1100); d_arrays = device table of narrays device pointers.
+ * The reference kernel has no bounds check: callers pad the arrays to a multiple of MAX_THREADS. */
+int ref_coincidencer(float** d_arrays, float* d_out, int narrays, size_t size, float thresh, int beam_thresh) {
+  REF_TRY
+  device_coincidencer(d_arrays, d_out, narrays, size, thresh, beam_thresh, MAX_BLOCKS, MAX_THREADS);
   REF_CATCH
 }
 

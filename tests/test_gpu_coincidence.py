@@ -1,6 +1,7 @@
-"""GPU parity of the multibeam coincidencer through the C ABI against
-oracle/coincidence.py: the matching kernel on random arrays (bit-exact) and the whole program on
-synthetic beams with interference common to all beams and a pulsar in one."""
+"""GPU parity of the multibeam coincidencer through the C ABI: the matching
+kernel against the unmodified reference kernel run on the same device buffers (oracle/_ref) and
+against oracle/coincidence.py (bit-exact), and the whole program on synthetic beams with
+interference common to all beams and a pulsar in one."""
 import ctypes as C
 import os
 
@@ -25,6 +26,37 @@ def test_coincidencer_kernel_bit_exact(lib, narrays, size, beam_thresh):
     pb.check(lib.ps_coincidencer(table.data_ptr(), out.data_ptr(), narrays, size, 1.5, beam_thresh, None))
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), K.match(arrs, 1.5, beam_thresh))
+
+
+@pytest.mark.parametrize("narrays,size,beam_thresh", [(1, 1000, 1), (4, 100003, 2), (13, 1 << 20, 4), (7, 5, 7), (6, 40000, 4)])
+def test_coincidencer_kernel_equals_reference_kernel(lib, ref, narrays, size, beam_thresh):
+    """Pin against the UNMODIFIED reference kernel run here: coincidence_kernel / device_coincidencer
+    (kernels.cu:1073-1100, forwarded by oracle/ref_harness.cu).  The reference kernel has no bounds
+    check (whole blocks of 512 threads run past `size`), so its buffers are padded to a multiple of
+    512; the first `size` mask values must be identical to ours, including values equal to the
+    threshold (strict >) and NaNs."""
+    rng = np.random.default_rng(size + narrays)
+    padded = (size + 511) // 512 * 512
+    arrs = []
+    for i in range(narrays):
+        a = rng.normal(0, 2, padded).astype(np.float32)
+        a[rng.integers(0, size, max(1, size // 50))] = np.float32(1.5)   # exactly at the threshold
+        if size > 100:
+            a[rng.integers(0, size, 3)] = np.nan
+        arrs.append(a)
+    d = [torch.from_numpy(a).cuda() for a in arrs]
+    table = torch.tensor([t.data_ptr() for t in d], dtype=torch.int64, device="cuda")
+    ours = torch.full((padded,), -1.0, dtype=torch.float32, device="cuda")
+    theirs = torch.full((padded,), -1.0, dtype=torch.float32, device="cuda")
+    pb.check(lib.ps_coincidencer(table.data_ptr(), ours.data_ptr(), narrays, size, 1.5, beam_thresh, None))
+    ref.ref_coincidencer.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_int]
+    assert ref.ref_coincidencer(table.data_ptr(), theirs.data_ptr(), narrays, size, 1.5, beam_thresh) == 0, ref.ref_last_error()
+    torch.cuda.synchronize()
+    assert torch.equal(ours[:size], theirs[:size])
+    from oracle import coincidence as K                                   # ... and so must the oracle's restatement
+    assert np.array_equal(theirs[:size].cpu().numpy(), K.match([a[:size] for a in arrs], 1.5, beam_thresh))
+    assert torch.all(ours[size:] == -1.0)                                # ours never writes past `size`
+    assert set(np.unique(ours[:size].cpu().numpy())) <= {0.0, 1.0}
 
 
 def test_coincidencer_rejects_empty(lib):

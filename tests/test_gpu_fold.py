@@ -99,6 +99,57 @@ def test_fold_optimise_matches_oracle(lib, optimiser, seed, drift, width):
     assert np.abs(op - want["opt_prof"]).max() <= 1e-5 * np.abs(want["opt_prof"]).max()
 
 
+@pytest.mark.parametrize("n,period,nbins,nints", [(1 << 17, 0.25, 32, 16), (1 << 17, 0.0123456, 32, 16), (100000, 0.0817, 16, 16),
+                                                  (1 << 20, 1.2345, 32, 8)])
+def test_fold_timeseries_equals_reference_kernel(lib, ref, n, period, nbins, nints):
+    """Pin against the UNMODIFIED reference kernel run here: fold_time_series_kernel (kernels.cu:597-632,
+    forwarded by oracle/ref_harness.cu).  The reference adds with float atomics in no fixed order and
+    without a barrier between clearing, adding to and reading its shared bins, so the comparison uses
+    inputs on which neither matters: small-integer samples (every partial sum is exact in float32,
+    whatever the order) and nbins <= 32, one warp per block, where the missing barrier cannot lose a
+    sample.  On such input the two kernels must agree bit for bit -- bins, hit counts (+1) and division."""
+    tsamp = 0.00032
+    rng = np.random.default_rng(n % 89 + nbins)
+    x = rng.integers(0, 16, n).astype(np.float32)
+    got = gpu_fold(lib, x, period, tsamp, nbins, nints)
+    d_in = dev(x)
+    d_out = torch.zeros(nints * nbins, dtype=torch.float32, device="cuda")
+    ref.ref_fold_timeseries.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_double, C.c_double, C.c_int]
+    assert ref.ref_fold_timeseries(d_in.data_ptr(), d_out.data_ptr(), n, nints, period, tsamp, nbins) == 0, ref.ref_last_error()
+    torch.cuda.synchronize()
+    want = d_out.cpu().numpy().reshape(nints, nbins)
+    assert np.array_equal(got, want)
+    assert got.std() > 0
+
+
+@pytest.mark.parametrize("seed,drift,width", [(1, 0.0, 3), (2, 9.0, 6), (3, -14.0, 1), (4, 25.0, 12), (5, -31.0, 20)])
+def test_fold_optimise_equals_reference_optimiser(lib, ref, optimiser, seed, drift, width):
+    """Pin against the reference's own FoldOptimiser object (folder.hpp:195-351: its kernels of
+    kernels.cu:655-865, three batched cuFFT plans, thrust::max_element) on the same folded
+    sub-integrations: same template, bin and optimised period; S/N, profile and optimised
+    sub-integrations to transform rounding."""
+    rng = np.random.default_rng(seed)
+    fold = rng.normal(0, 1, (16, 64)).astype(np.float32) * 100
+    for s in range(16):
+        start = int(round(20 + drift * s / 16.0))
+        fold[s, (start + np.arange(width)) % 64] += 600
+    period, tobs = 0.0731, np.float32(41.94304)
+    res, of, op = gpu_optimise(lib, optimiser, fold, period, tobs)
+    d = dev(fold.ravel())
+    sn, per, wid, obin = C.c_float(), C.c_double(), C.c_int(), C.c_int()
+    rof = np.zeros((16, 64), np.float32)
+    rop = np.zeros(64, np.float32)
+    ref.ref_fold_optimise.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_double, C.c_float, C.POINTER(C.c_float),
+                                      C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
+    assert ref.ref_fold_optimise(d.data_ptr(), 64, 16, period, tobs, C.byref(sn), C.byref(per), C.byref(wid), C.byref(obin),
+                                 rof.ctypes.data, rop.ctypes.data) == 0, ref.ref_last_error()
+    assert (res.opt_width, res.opt_bin) == (wid.value, obin.value)
+    assert np.float32(res.opt_period) == np.float32(per.value)      # the reference's getter narrows to float
+    assert res.opt_sn == pytest.approx(sn.value, rel=1e-3)
+    assert np.abs(of - rof).max() <= 1e-4 * np.abs(rof).max()
+    assert np.abs(op - rop).max() <= 1e-4 * np.abs(rop).max()
+
+
 def test_fold_optimise_is_repeatable(lib, optimiser):
     rng = np.random.default_rng(11)
     fold = rng.normal(0, 1, (16, 64)).astype(np.float32)

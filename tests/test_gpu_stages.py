@@ -273,6 +273,32 @@ def test_divide_and_zap(lib, oracle, request):
     assert torch.equal(rX, dX)
 
 
+@pytest.mark.parametrize("size", [1 << 20, 1 << 23])
+def test_zap_47tuc_zaplist_vs_reference(lib, oracle, ref, size):
+    """The reference's survey zaplist misc/47tuc.zaplist (104 birdies, kept as tests/golden/47tuc.zaplist)
+    through ps_zap_birdies against zap_birdies_kernel of the unmodified reference build
+    (kernels.cu:1036-1069) and the oracle: bit-exact, including birdies whose range is clipped at the
+    spectrum's ends."""
+    import os
+    from conftest import GOLDEN
+    zl = np.loadtxt(os.path.join(GOLDEN, "47tuc.zaplist"), dtype=np.float32)
+    assert zl.shape == (104, 2)
+    cfg = oracle.SearchConfig(size, 64e-6)
+    nb = cfg.nbins
+    rng = np.random.default_rng(47)
+    X = (rng.standard_normal(nb) + 1j * rng.standard_normal(nb)).astype(np.complex64)
+    dX, rX = dev(X.view(np.float32)), dev(X.view(np.float32))
+    db, dw = dev(zl[:, 0]), dev(zl[:, 1])
+    check(lib.ps_zap_birdies(ptr(dX), ptr(db), ptr(dw), cfg.bin_width_f, 104, nb, None))
+    ref.ref_zap_birdies.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_uint, C.c_uint]
+    rcheck(ref, ref.ref_zap_birdies(ptr(rX), ptr(db), ptr(dw), cfg.bin_width_f, 104, nb))
+    torch.cuda.synchronize()
+    assert torch.equal(dX, rX)
+    got = dX.cpu().numpy().view(np.complex64)
+    assert np.array_equal(got, oracle.zap(X, zl[:, 0], zl[:, 1], cfg.bin_width_f))
+    assert (got == 1).sum() >= 104
+
+
 # ------------------------------------------------------------------ stats / fill / convert
 def test_stats_fill_convert(lib, oracle, request):
     n = 4194305
