@@ -99,7 +99,7 @@ def test_fold_optimise_matches_oracle(lib, optimiser, seed, drift, width):
     assert np.abs(op - want["opt_prof"]).max() <= 1e-5 * np.abs(want["opt_prof"]).max()
 
 
-@pytest.mark.parametrize("n,period,nbins,nints", [(1 << 17, 0.25, 32, 16), (1 << 17, 0.0123456, 32, 16), (100000, 0.0817, 16, 16),
+@pytest.mark.parametrize("n,period,nbins,nints", [(1 << 17, 0.25, 32, 16), (1 << 17, 0.0123456, 32, 16), (102400, 0.0817, 16, 16),
                                                   (1 << 20, 1.2345, 32, 8)])
 def test_fold_timeseries_equals_reference_kernel(lib, ref, n, period, nbins, nints):
     """Pin against the UNMODIFIED reference kernel run here: fold_time_series_kernel (kernels.cu:597-632,
@@ -107,7 +107,10 @@ def test_fold_timeseries_equals_reference_kernel(lib, ref, n, period, nbins, nin
     without a barrier between clearing, adding to and reading its shared bins, so the comparison uses
     inputs on which neither matters: small-integer samples (every partial sum is exact in float32,
     whatever the order) and nbins <= 32, one warp per block, where the missing barrier cannot lose a
-    sample.  On such input the two kernels must agree bit for bit -- bins, hit counts (+1) and division."""
+    sample; and sub-integrations that are a whole number of nbins-sample strides, because the
+    reference's last block otherwise reads up to nbins-1 samples past the end of the series (ours
+    clamps there).  On such input the two kernels must agree bit for bit -- bins, hit counts (+1)
+    and division."""
     tsamp = 0.00032
     rng = np.random.default_rng(n % 89 + nbins)
     x = rng.integers(0, 16, n).astype(np.float32)
