@@ -76,6 +76,10 @@ struct CoincidenceOptions {  // CmdLineOptions of coincidencer.cpp:30-44 (the fi
 };
 
 // main() of src/coincidencer.cpp:122-214.  Masks are also handed back when the pointers are set.
+// PROVENANCE: interface mirror, not implementation.  Statement order and local names
+// (tim_host_ptr_array, ccder, pspecs, ...) follow the reference's main() line for line -- it is the
+// calling sequence of the transform classes that tests/test_boundary_compile.py compiles verbatim;
+// the work is csrc/coincidence.cu, csrc/bluestein.cu and the staged entry points behind the C ABI.
 inline void coincidence_match_files(const std::vector<std::string>& files, const CoincidenceOptions& args, std::vector<float>* samp_mask_out,
                                     std::vector<float>* spec_mask_out) {
   int nfiles = (int)files.size();

@@ -3,6 +3,8 @@
 // names so that pipeline code written against the reference compiles against this header.
 // Device buffers are owned RAII-style exactly like the reference (ctor cudaMalloc, dtor
 // cudaFree: fourierseries.hpp:123-132, timeseries.hpp:239-243,294-297).
+// PROVENANCE: interface mirror.  Class, method and member names are the reference's by requirement
+// ("keep the API"); the containers hold no arithmetic.
 #pragma once
 #include <cuda_runtime.h>
 #include <algorithm>

@@ -92,6 +92,11 @@ class FoldOptimiser {  // folder.hpp:65-352
   }
 };
 
+// PROVENANCE: interface mirror, not implementation.  The constructor, fold_all_mapped() and fold_n()
+// below keep the statement order and the local names of the reference's MultiFolder
+// (include/transforms/folder.hpp:352-434), and FoldedSubints above those of data_types/folded.hpp:10-74,
+// because north_star requires the reference's API and call order; only the progress bar is gone.
+// They contain no arithmetic: folding and optimisation are csrc/fold.cu behind the C ABI.
 class MultiFolder {  // folder.hpp:354-460
   std::vector<Candidate>& cands;
   DispersionTrials<unsigned char>& dm_trials;
