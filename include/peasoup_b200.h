@@ -342,6 +342,14 @@ int ps_peak_range(int nbins, double bin_width, int nh, float min_freq, float max
  * in: n candidates (is_top ignored); out: flattened survivors (+ assoc if keep_related). */
 long ps_distill(int kind, float tol, float max_harm_or_tobs, int keep_related, int fractional_harms,
                 const ps_candidate* in, long n, ps_candidate* out, long max_out);
+/* The two distillations after the workers have joined (src/pipeline_multi.cu:353-365:
+ * DMDistiller(freq_tol, true) then HarmonicDistiller(freq_tol, max_harm, true, false)) on the MERGED
+ * per-DM candidate list.  in: flattened records as ps_pipeline_run / ps_pipeline_search return them
+ * (is_top = 1 starts a candidate, its acceleration associates follow), in ascending dm_idx order --
+ * after a multi-GPU run that is the gathered list in canonical order.  out: the surviving
+ * candidates flattened depth-first.  Returns the number of records (may exceed max_out: call again). */
+long ps_distill_merged(const ps_candidate* in, long n, float freq_tol, int max_harm, ps_candidate* out,
+                       long max_out);
 
 #ifdef __cplusplus
 }

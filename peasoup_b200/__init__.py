@@ -74,7 +74,7 @@ SYMBOLS = [
     "ps_dedisperse", "ps_search_filterbank", "ps_fold_timeseries", "ps_fold_optimiser_create",
     "ps_fold_optimiser_destroy", "ps_fold_optimise", "ps_fold_results_last", "ps_coincidencer",
     "ps_coincidence_files",
-    "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill",
+    "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill", "ps_distill_merged",
 ]
 
 
@@ -140,6 +140,7 @@ def load() -> C.CDLL:
         "ps_cluster_peaks": [vp, vp, i, i, vp, vp],
         "ps_peak_range": [i, d, i, f, f, C.POINTER(i), C.POINTER(i), C.POINTER(f)],
         "ps_distill": [i, f, f, i, i, vp, C.c_long, vp, C.c_long],
+        "ps_distill_merged": [vp, C.c_long, f, i, vp, C.c_long],
     }
     for name, args in sig.items():
         getattr(lib, name).argtypes = args
@@ -157,6 +158,7 @@ def load() -> C.CDLL:
     lib.ps_dedisp_max_delay.restype = C.c_long
     lib.ps_pipeline_close.restype = None
     lib.ps_distill.restype = C.c_long
+    lib.ps_distill_merged.restype = C.c_long
     lib.ps_fold_results_last.restype = C.c_long
     lib.ps_coincidence_files.restype = C.c_long
     lib.ps_fold_optimiser_destroy.restype = None

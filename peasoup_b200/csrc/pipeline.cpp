@@ -278,6 +278,29 @@ long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, 
   }
 }
 
+// pipeline_multi.cu:353-365 on a merged, flattened per-DM list
+long ps_distill_merged(const ps_candidate* in, long n, float freq_tol, int max_harm, ps_candidate* out, long max_out) {
+  try {
+    if (n < 0 || (n > 0 && !in)) ErrorChecker::throw_error("ps_distill_merged: null argument");
+    std::vector<Candidate> dm_cands;
+    for (long i = 0; i < n; i++) {
+      Candidate c(in[i].dm, in[i].dm_idx, in[i].acc, in[i].nh, in[i].snr, in[i].freq);
+      if (in[i].is_top || dm_cands.empty())
+        dm_cands.push_back(c);
+      else
+        dm_cands.back().append(c);
+    }
+    DMDistiller dm_still(freq_tol, true);
+    HarmonicDistiller harm_still(freq_tol, (float)max_harm, true, false);
+    dm_cands = dm_still.distill(dm_cands);
+    dm_cands = harm_still.distill(dm_cands);
+    return flatten(dm_cands, out, max_out);
+  } catch (std::exception& e) {
+    ps::set_error(e.what());
+    return PS_ECUDA;
+  }
+}
+
 // main() of src/coincidencer.cpp
 long ps_coincidence_files(const char* const* filenames, int nfiles, const ps_coincidence_params* p, float* h_samp_mask,
                           size_t max_samp, float* h_spec_mask, size_t max_spec) {

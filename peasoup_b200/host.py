@@ -152,6 +152,18 @@ def distill(kind, cands: np.ndarray, tol, max_harm_or_tobs, keep_related, fracti
         cap = n
 
 
+def distill_merged(recs: np.ndarray, freq_tol=1e-4, max_harm=16) -> np.ndarray:
+    """DMDistiller + HarmonicDistiller on the merged per-DM list (pipeline_multi.cu:353-365)."""
+    c = np.ascontiguousarray(recs, CAND_DTYPE)
+    cap = max(16, len(c) + 16)
+    while True:
+        out = np.zeros(cap, CAND_DTYPE)
+        n = check(load().ps_distill_merged(ptr(c), len(c), freq_tol, int(max_harm), ptr(out), cap))
+        if n <= cap:
+            return out[:n].copy()
+        cap = n
+
+
 def pipeline_search(trials_u8, dm_list, params: PipelineParams, accs=None, zap=None, device0=0, nworkers=1,
                     dm_idx_offset=0, max_out=1 << 20):
     """ps_pipeline_search: host u8 trials [ndm][nsamps] -> flattened candidate records.

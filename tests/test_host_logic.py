@@ -88,3 +88,29 @@ def test_distillers(lib, oracle, kind, p2, keep, frac, n):
         if not keep:
             assert a["is_top"].all()
         assert len(a) >= (1 if n else 0)
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 40, 300])
+def test_distill_merged_vs_oracle_finalise(lib, oracle, n):
+    """ps_distill_merged = the two distillations after the workers joined (pipeline_multi.cu:353-365) on
+    a merged per-DM list whose entries carry acceleration associates, against the oracle's finalise()
+    (itself compared with the golden tutorial run through test_tutorial_final_list_vs_oracle_postprocess).
+    Distinct S/N values: the reference's std::sort is unstable, ties have no defined order."""
+    from peasoup_b200.host import distill_merged
+    rng = np.random.default_rng(100 + n)
+    c = random_cands(rng, n)
+    c["snr"] = (9 + np.arange(n)[rng.permutation(n)] * 0.37).astype(np.float32)
+    c["is_top"] = 1
+    if n > 3:                                    # every third record becomes an associate of its predecessor
+        c["is_top"][2::3] = 0
+        c["dm_idx"] = np.sort(c["dm_idx"])
+    a = distill_merged(c, 1e-4, 16)
+    b = oracle.finalise(c, 1e-4, 16, 10 ** 9)
+    # nothing is dropped: non-unique candidates become associates -- more than once when several harmonic
+    # ratios match, because the reference's HarmonicDistiller does not break after a match (SURVEY 9.6)
+    assert len(a) == len(b) >= n
+    for name in CAND_DTYPE.names:
+        assert np.array_equal(a[name], b[name]), name
+    if n:
+        tops = a[a["is_top"] == 1]
+        assert np.all(np.diff(tops["snr"]) <= 0)  # survivors come out in descending S/N
