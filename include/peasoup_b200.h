@@ -69,6 +69,10 @@ int ps_peak_workspace_create(size_t max_peaks, ps_peak_workspace** out);
 void ps_peak_workspace_destroy(ps_peak_workspace* ws);
 int ps_find_peaks(int n, int start, const float* d_dat, float thresh, int* h_idx, float* h_snr,
                   size_t max_out, ps_peak_workspace* ws, void* stream);
+/* Number of above-threshold bins the last ps_find_peaks call on this workspace counted -- after
+ * PS_EOVERFLOW, the capacity a new workspace needs (the reference has no such path: its
+ * PeakFinder writes past its fixed 100000-entry host arrays, peakfinder.hpp:59-70,84). */
+size_t ps_peak_workspace_needed(const ps_peak_workspace* ws);
 
 /* median_scrunch5 / linear_stretch, kernels.h:252,256 / kernels.cu:875-1011. */
 int ps_median_scrunch5(const float* d_in, size_t count, float* d_out, void* stream);
@@ -170,8 +174,8 @@ long ps_search_fetch_peaks(ps_search* s, ps_raw_peak* h_out, size_t max_out, voi
  * and a way to enlarge the device list to hold them (synchronises the device; the list's content is
  * lost, so the caller resets the peaks and repeats ps_search_accel_batch -- the whitened series is
  * still there).  The pipeline driver does exactly that, so a DM trial full of interference costs
- * time instead of failing; the reference silently truncates at 100000 peaks per spectrum
- * (peakfinder.hpp:59-70). */
+ * time instead of failing; the reference has no overflow handling: beyond 100000 above-threshold
+ * bins per spectrum it writes past its host arrays (peakfinder.hpp:59-70,84). */
 unsigned ps_search_peaks_needed(ps_search* s);
 int ps_search_reserve_peaks(ps_search* s, unsigned max_peaks);
 /* The harmonic-sum + threshold + compaction stage on its own (HarmonicFolder::fold +
@@ -259,6 +263,15 @@ long ps_dedisp_max_delay(const float* h_dm_list, int ndm, int nchans, float dt, 
 int ps_dedisperse(const unsigned char* h_in, size_t nsamps, int nchans, int nbits, float dt, float f0,
                   float df, const float* h_dm_list, int ndm, const int* h_killmask,
                   unsigned char* h_out, size_t nout);
+/* The same on a given device (dedisp_create_plan_multi's device index, dedisperser.hpp:21-30;
+ * device < 0: the current one) and with a cap on the device memory it may hold (0: 60 % of what is
+ * free).  The observation is processed in time gulps of as many samples as fit -- packed input,
+ * unpacked copy and ndm output rows per gulp -- like dedisp's own gulping, so long files and long DM
+ * lists take more gulps instead of failing to allocate.  Channel frequencies must descend from f0
+ * (df < 0) and the DM list must be non-negative and ascending: delays are unsigned sample counts. */
+int ps_dedisperse_on(int device, size_t max_device_bytes, const unsigned char* h_in, size_t nsamps,
+                     int nchans, int nbits, float dt, float f0, float df, const float* h_dm_list, int ndm,
+                     const int* h_killmask, unsigned char* h_out, size_t nout);
 
 typedef struct {
   ps_pipeline_params pipe;  /* search.size = --fft_size (0: prev_power_of_two); nsamps, tsamp, cfreq, foff come from the file */

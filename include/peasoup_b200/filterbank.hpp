@@ -124,11 +124,15 @@ class Dedisperser {  // dedisperser.hpp:12-114
   std::vector<float> dm_list;
   std::vector<int> killmask;
   std::vector<unsigned char> trials_storage;
+  int device = -1;  // -1: the current device
 
  public:
   Dedisperser(Filterbank& filterbank, unsigned int /*num_gpus*/ = 1) : filterbank(filterbank) {
     killmask.assign(filterbank.get_nchans(), 1);
   }
+  // the reference's plan takes device indices 0..num_gpus-1 (dedisp_create_plan_multi); here the caller
+  // names the device the trials are dedispersed on
+  void set_device(int d) { device = d; }
   void set_dm_list(std::vector<float> v) { dm_list = v; }
   void set_dm_list(float* p, unsigned int n) { dm_list.assign(p, p + n); }
   std::vector<float> get_dm_list() { return dm_list; }
@@ -162,7 +166,7 @@ class Dedisperser {  // dedisperser.hpp:12-114
     if (max_delay >= (long)filterbank.get_nsamps()) ErrorChecker::throw_error("Dedisperser: max delay exceeds the data length");
     unsigned int out_nsamps = filterbank.get_nsamps() - (unsigned int)max_delay;
     trials_storage.resize((size_t)out_nsamps * dm_list.size());
-    ErrorChecker::check(ps_dedisperse(filterbank.get_data(), filterbank.get_nsamps(), filterbank.get_nchans(), filterbank.get_nbits(),
+    ErrorChecker::check(ps_dedisperse_on(device, 0, filterbank.get_data(), filterbank.get_nsamps(), filterbank.get_nchans(), filterbank.get_nbits(),
                                       filterbank.get_tsamp(), filterbank.get_fch1(), filterbank.get_foff(), &dm_list[0],
                                       (int)dm_list.size(), &killmask[0], trials_storage.data(), out_nsamps));
     return DispersionTrials<unsigned char>(trials_storage.data(), out_nsamps, filterbank.get_tsamp(), dm_list);

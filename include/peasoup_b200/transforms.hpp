@@ -222,15 +222,22 @@ class PeakFinder {
   std::vector<float> snrs, peaksnrs, peakfreqs;
   ps_peak_workspace* ws;
 
- public:
-  PeakFinder(float threshold, float min_freq, float max_freq, unsigned int /*size*/, int min_gap = 30)
-      : threshold(threshold), min_freq(min_freq), max_freq(max_freq), min_gap(min_gap), max_cands(100000), ws(0) {
+  void reserve(unsigned int n) {
+    if (ws) ps_peak_workspace_destroy(ws);
+    ws = 0;
+    max_cands = n;
     idxs.resize(max_cands);
     snrs.resize(max_cands);
     peakidxs.resize(max_cands);
     peaksnrs.resize(max_cands);
     peakfreqs.resize(max_cands);
     ErrorChecker::check(ps_peak_workspace_create(max_cands, &ws));
+  }
+
+ public:
+  PeakFinder(float threshold, float min_freq, float max_freq, unsigned int /*size*/, int min_gap = 30, unsigned int max_cands_ = 100000)
+      : threshold(threshold), min_freq(min_freq), max_freq(max_freq), min_gap(min_gap), max_cands(max_cands_), ws(0) {
+    reserve(max_cands_);
   }
   ~PeakFinder() { ps_peak_workspace_destroy(ws); }
   PeakFinder(const PeakFinder&) = delete;
@@ -241,8 +248,13 @@ class PeakFinder {
   void find_candidates(DevicePowerSpectrum<float>& pspec, SpectrumCandidates& cands) {
     int nh = pspec.get_nh();
     PeakRange r = peak_range((int)pspec.get_nbins(), pspec.get_bin_width(), nh, min_freq, max_freq);
-    // the reference overruns its 100000-entry host arrays silently; here overflow is an error
+    // the reference overruns its 100000-entry host arrays silently; here the workspace grows to 1.5x
+    // the count found and the spectrum is searched again (as the fused path does with its peak list)
     int count = ps_find_peaks(r.limit, r.start_idx, pspec.get_data(), threshold, &idxs[0], &snrs[0], max_cands, ws, 0);
+    if (count == PS_EOVERFLOW) {
+      reserve((unsigned int)(ps_peak_workspace_needed(ws) + ps_peak_workspace_needed(ws) / 2 + 16));
+      count = ps_find_peaks(r.limit, r.start_idx, pspec.get_data(), threshold, &idxs[0], &snrs[0], max_cands, ws, 0);
+    }
     ErrorChecker::check(count);
     int npeaks = cluster_peaks(&idxs[0], &snrs[0], count, min_gap, &peakidxs[0], &peaksnrs[0]);
     for (int i = 0; i < npeaks; i++) peakfreqs[i] = peakidxs[i] * r.factor;

@@ -62,7 +62,7 @@ class Candidate(C.Structure):
 SYMBOLS = [
     "ps_last_error", "ps_version", "ps_resampleII", "ps_resample", "ps_resample_index_map",
     "ps_form_power_series", "ps_normalise", "ps_harmonic_sum", "ps_peak_workspace_create",
-    "ps_peak_workspace_destroy", "ps_find_peaks", "ps_median_scrunch5", "ps_linear_stretch",
+    "ps_peak_workspace_destroy", "ps_find_peaks", "ps_peak_workspace_needed", "ps_median_scrunch5", "ps_linear_stretch",
     "ps_running_median", "ps_running_median_noalloc", "ps_divide_c_by_f", "ps_zap_birdies", "ps_rms", "ps_mean", "ps_fill",
     "ps_convert_u8_f32", "ps_fft_plan_create", "ps_fft_plan_destroy", "ps_fft_r2c", "ps_fft_c2r",
     "ps_search_create", "ps_search_destroy", "ps_search_set_zaplist", "ps_search_whiten",
@@ -71,7 +71,7 @@ SYMBOLS = [
     "ps_search_harmonic_peaks", "ps_search_resample_index_map", "ps_search_whitened_series", "ps_search_last_spectrum", "ps_launch_count", "ps_count_transfer",
     "ps_transfer_bytes", "ps_pipeline_search", "ps_pipeline_profile", "ps_pipeline_open",
     "ps_pipeline_run", "ps_pipeline_close", "ps_dedisp_generate_dm_list", "ps_dedisp_max_delay",
-    "ps_dedisperse", "ps_search_filterbank", "ps_fold_timeseries", "ps_fold_optimiser_create",
+    "ps_dedisperse", "ps_dedisperse_on", "ps_search_filterbank", "ps_fold_timeseries", "ps_fold_optimiser_create",
     "ps_fold_optimiser_destroy", "ps_fold_optimise", "ps_fold_results_last", "ps_coincidencer",
     "ps_coincidence_files",
     "ps_accel_plan_generate", "ps_cluster_peaks", "ps_peak_range", "ps_distill", "ps_distill_merged",
@@ -129,6 +129,7 @@ def load() -> C.CDLL:
         "ps_dedisp_generate_dm_list": [f, f, f, f, f, f, i, f, vp, i],
         "ps_dedisp_max_delay": [vp, i, i, f, f, f],
         "ps_dedisperse": [vp, sz, i, i, f, f, f, vp, i, vp, vp, sz],
+        "ps_dedisperse_on": [i, sz, vp, sz, i, i, f, f, f, vp, i, vp, vp, sz],
         "ps_search_filterbank": [C.c_char_p, C.POINTER(FilterbankParams), vp, C.c_long, vp, i, C.POINTER(i), vp],
         "ps_fold_timeseries": [vp, vp, sz, sz, d, d, i, vp],
         "ps_fold_optimiser_create": [u, u, C.POINTER(vp)], "ps_fold_optimiser_destroy": [vp],
@@ -165,6 +166,8 @@ def load() -> C.CDLL:
     lib.ps_search_whitened_series.restype = vp
     lib.ps_search_last_spectrum.restype = vp
     lib.ps_peak_workspace_destroy.restype = None
+    lib.ps_peak_workspace_needed.argtypes = [vp]
+    lib.ps_peak_workspace_needed.restype = C.c_size_t
     lib.ps_fft_plan_destroy.restype = None
     lib.ps_search_destroy.restype = None
     _lib = lib

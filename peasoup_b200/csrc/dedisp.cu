@@ -13,6 +13,7 @@
 // sample, channel-major, so that the dedispersion kernel's loads are contiguous in time;
 // dedisperse_kernel sums the delayed channels for (DM trial, eight time samples) with packed
 // 16-bit adds and scales to 8 bits.
+#include <algorithm>
 #include <cmath>
 #include <vector>
 #include "common.cuh"
@@ -147,48 +148,99 @@ long ps_dedisp_max_delay(const float* h_dm_list, int ndm, int nchans, float dt, 
   return (long)(h_dm_list[ndm - 1] * tab[nchans - 1] + 0.5f);
 }
 
-int ps_dedisperse(const unsigned char* h_in, size_t nsamps, int nchans, int nbits, float dt, float f0, float df,
-                  const float* h_dm_list, int ndm, const int* h_killmask, unsigned char* h_out, size_t nout) {
+// One time gulp at a time: gulp g covers output samples [t0, t0 + G) and needs input samples
+// [t0, t0 + G + max_delay).  Device memory held: the packed gulp, its one-byte-per-sample unpacked
+// copy (4-8x the packed size for 1/2-bit data) and the ndm x G output block -- sized from the free
+// memory of the device (or max_device_bytes), so a long observation or a long DM list costs more
+// gulps, not a failed cudaMalloc.  dedisp gulps the same way (its gulp_size); every output sample is
+// computed exactly as in the single-gulp case.
+int ps_dedisperse_on(int device, size_t max_device_bytes, const unsigned char* h_in, size_t nsamps, int nchans, int nbits, float dt,
+                     float f0, float df, const float* h_dm_list, int ndm, const int* h_killmask, unsigned char* h_out, size_t nout) {
   if (nbits != 1 && nbits != 2 && nbits != 4 && nbits != 8) return invalid("ps_dedisperse: nbits must be 1, 2, 4 or 8");
   if (ndm <= 0 || nchans <= 0 || !nsamps) return invalid("ps_dedisperse: empty input");
-  long max_delay = ps_dedisp_max_delay(h_dm_list, ndm, nchans, dt, f0, df);
-  if ((size_t)max_delay >= nsamps || nout != nsamps - (size_t)max_delay)
-    return invalid("ps_dedisperse: nout must equal nsamps - max_delay");
   std::vector<float> tab;
   delay_table_host(tab, nchans, dt, f0, df);
-  size_t in_bytes = nsamps * nchans * nbits / 8;
-  const size_t pitch = (nsamps + 16 + 15) & ~(size_t)15;  // U rows: word-aligned, 16 readable bytes past the end
-  const size_t opitch = (nout + 7) & ~(size_t)7;          // trial rows on the device: whole 8-sample groups
+  // delays are unsigned sample counts (dedisp's delay table is relative to the FIRST, highest-frequency
+  // channel): a band given in ascending order, or a negative DM, would need samples before the start
+  for (int i = 0; i < ndm; i++)
+    for (int c = 0; c < nchans; c++)
+      if (h_dm_list[i] * tab[c] < -0.5f)
+        return invalid("ps_dedisperse: negative delay (channel frequencies must descend from fch1, DM trials must be >= 0)");
+  long max_delay = ps_dedisp_max_delay(h_dm_list, ndm, nchans, dt, f0, df);
+  for (int i = 0; i < ndm; i++)  // the list need not be sorted: the largest delay of any trial and channel
+    for (int c = 0; c < nchans; c++) max_delay = std::max(max_delay, (long)(h_dm_list[i] * tab[c] + 0.5f));
+  if (max_delay != ps_dedisp_max_delay(h_dm_list, ndm, nchans, dt, f0, df))
+    return invalid("ps_dedisperse: the DM list must ascend (dedisp takes max_delay from its last entry)");
+  if ((size_t)max_delay >= nsamps || nout != nsamps - (size_t)max_delay)
+    return invalid("ps_dedisperse: nout must equal nsamps - max_delay");
+  int prev_device = -1;
+  if (device >= 0) {
+    PS_CUDA(cudaGetDevice(&prev_device), "ps_dedisperse");
+    PS_CUDA(cudaSetDevice(device), "ps_dedisperse");
+  }
+  struct Restore {
+    int d;
+    ~Restore() { if (d >= 0) cudaSetDevice(d); }
+  } restore{prev_device};
+
+  // gulp length: multiple of 64 output samples (packed bytes and 8-sample groups stay aligned)
+  size_t budget = max_device_bytes;
+  if (!budget) {
+    size_t free_b = 0, total_b = 0;
+    PS_CUDA(cudaMemGetInfo(&free_b, &total_b), "ps_dedisperse");
+    budget = free_b / 10 * 6;
+  }
+  const double per_sample = (double)nchans * nbits / 8.0 + (double)nchans + (double)ndm;   // packed + unpacked + output
+  const double fixed = (double)max_delay * ((double)nchans * nbits / 8.0 + (double)nchans) + 64.0 * nchans + (1 << 20);
+  size_t gulp = nout;
+  if (fixed + per_sample * (double)gulp > (double)budget) {
+    if ((double)budget <= fixed + per_sample * 64.0) return invalid("ps_dedisperse: not enough device memory for one 64-sample gulp");
+    gulp = (size_t)(((double)budget - fixed) / per_sample) / 64 * 64;
+  }
+  const size_t gin = gulp + (size_t)max_delay;                  // input samples per gulp
+  const size_t pitch = (gin + 16 + 15) & ~(size_t)15;           // U rows: word-aligned, 16 readable bytes past the end
+  const size_t opitch = (gulp + 7) & ~(size_t)7;                // trial rows on the device: whole 8-sample groups
+  const size_t in_cap = (gin * nchans * nbits + 7) / 8;
   unsigned char *d_in = 0, *d_U = 0, *d_out = 0;
   float *d_tab = 0, *d_dm = 0;
   int* d_kill = 0;
-  cudaError_t e = cudaMalloc(&d_in, in_bytes);
+  cudaError_t e = cudaMalloc(&d_in, in_cap);
   if (e == cudaSuccess) e = cudaMalloc(&d_U, (size_t)nchans * pitch + 16);
-  if (e == cudaSuccess) e = cudaMemset(d_U, 0, (size_t)nchans * pitch + 16);
   if (e == cudaSuccess) e = cudaMalloc(&d_out, (size_t)ndm * opitch);
   if (e == cudaSuccess) e = cudaMalloc(&d_tab, sizeof(float) * nchans);
   if (e == cudaSuccess) e = cudaMalloc(&d_dm, sizeof(float) * ndm);
   if (e == cudaSuccess && h_killmask) e = cudaMalloc(&d_kill, sizeof(int) * nchans);
-  if (e == cudaSuccess) e = cudaMemcpy(d_in, h_in, in_bytes, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(d_tab, tab.data(), sizeof(float) * nchans, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(d_dm, h_dm_list, sizeof(float) * ndm, cudaMemcpyHostToDevice);
   if (e == cudaSuccess && h_killmask) e = cudaMemcpy(d_kill, h_killmask, sizeof(int) * nchans, cudaMemcpyHostToDevice);
-  int rc = PS_OK;
-  if (e == cudaSuccess) {
-    dim3 g1((unsigned)((nsamps + 31) / 32), (unsigned)((nchans + 31) / 32));
-    unpack_transpose_kernel<<<g1, 256>>>(d_in, d_U, d_kill, nbits, nchans, nsamps, pitch);
+  const float in_range = (float)((1 << nbits) - 1);
+  const float factor = ((3.f * 1024.f) / 255.f) / 16.f;
+  for (size_t t0 = 0; e == cudaSuccess && t0 < nout; t0 += gulp) {
+    const size_t g_out = std::min(gulp, nout - t0);            // output samples of this gulp
+    const size_t g_in = g_out + (size_t)max_delay;              // <= nsamps - t0
+    const size_t first_bit = t0 * (size_t)nchans * nbits;       // t0 is a multiple of 64: byte-aligned
+    const size_t bytes = (g_in * nchans * nbits + 7) / 8;
+    e = cudaMemcpy(d_in, h_in + first_bit / 8, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_U, 0, (size_t)nchans * pitch + 16);
+    if (e != cudaSuccess) break;
+    dim3 g1((unsigned)((g_in + 31) / 32), (unsigned)((nchans + 31) / 32));
+    unpack_transpose_kernel<<<g1, 256>>>(d_in, d_U, d_kill, nbits, nchans, g_in, pitch);
     g_launches.fetch_add(1);
-    dim3 g2((unsigned)ndm, (unsigned)std::min<size_t>((nout / 8 + 255) / 256 + 1, 65535));
-    float in_range = (float)((1 << nbits) - 1);
-    float factor = ((3.f * 1024.f) / 255.f) / 16.f;
-    dedisperse_kernel<<<g2, 256, sizeof(unsigned) * nchans>>>(d_U, d_tab, d_dm, d_out, nchans, pitch, nout, opitch, in_range, factor);
+    dim3 g2((unsigned)ndm, (unsigned)std::min<size_t>((g_out / 8 + 255) / 256 + 1, 65535));
+    dedisperse_kernel<<<g2, 256, sizeof(unsigned) * nchans>>>(d_U, d_tab, d_dm, d_out, nchans, pitch, g_out, opitch, in_range, factor);
     g_launches.fetch_add(1);
     e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpy2D(h_out, nout, d_out, opitch, nout, ndm, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy2D(h_out + t0, nout, d_out, opitch, g_out, ndm, cudaMemcpyDeviceToHost);
   }
+  int rc = PS_OK;
   if (e != cudaSuccess) rc = cuda_fail(e, "ps_dedisperse");
   cudaFree(d_in); cudaFree(d_U); cudaFree(d_out); cudaFree(d_tab); cudaFree(d_dm); cudaFree(d_kill);
   return rc;
+}
+
+int ps_dedisperse(const unsigned char* h_in, size_t nsamps, int nchans, int nbits, float dt, float f0, float df,
+                  const float* h_dm_list, int ndm, const int* h_killmask, unsigned char* h_out, size_t nout) {
+  return ps_dedisperse_on(-1, 0, h_in, nsamps, nchans, nbits, dt, f0, df, h_dm_list, ndm, h_killmask, h_out, nout);
 }
 
 }  // extern "C"

@@ -190,6 +190,7 @@ long ps_search_filterbank(const char* filename, const ps_filterbank_params* fp, 
     clk::time_point t1 = clk::now();
     const int nworkers = fp->nworkers < 1 ? 1 : fp->nworkers;
     Dedisperser dedisperser(filobj, nworkers);
+    dedisperser.set_device(fp->device0);
     if (fp->killfile && fp->killfile[0]) dedisperser.set_killmask(std::string(fp->killfile));
     dedisperser.generate_dm_list(fp->dm_start, fp->dm_end, fp->dm_pulse_width, fp->dm_tol);
     std::vector<float> dm_list = dedisperser.get_dm_list();

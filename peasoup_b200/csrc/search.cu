@@ -776,6 +776,9 @@ const float* ps_search_whitened_series(ps_search* hs) {
   if (!s) return nullptr;
   const ps_fft_plan_t* p = s->plan;
   if (!s->d_tim_nat && cudaMalloc(&s->d_tim_nat, sizeof(float) * s->prm.size) != cudaSuccess) return nullptr;
+  // the whitening may still be running on a caller's non-blocking stream: the copy below is launched on the
+  // default stream, so wait for the device first
+  if (cudaDeviceSynchronize() != cudaSuccess) return nullptr;
   untranspose_pairs_kernel<<<ew_grid(p->M, 256, 2), 256>>>(reinterpret_cast<const float2*>(s->d_tim),
                                                            reinterpret_cast<float2*>(s->d_tim_nat), p->M, s->col_len, s->lg_n2);
   g_launches.fetch_add(1);

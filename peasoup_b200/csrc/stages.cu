@@ -362,6 +362,7 @@ struct ps_peak_workspace {
   std::vector<std::pair<int, float>> tmp;
   std::vector<int> hi;
   std::vector<float> hs;
+  size_t needed = 0;  // above-threshold count of the last ps_find_peaks call
 };
 
 int ps_peak_workspace_create(size_t max_peaks, ps_peak_workspace** out) {
@@ -405,6 +406,7 @@ int ps_find_peaks(int n, int start, const float* d_dat, float thresh, int* h_idx
   unsigned count = 0;
   PS_CUDA(cudaMemcpyAsync(&count, ws->d_count, sizeof(unsigned), cudaMemcpyDeviceToHost, st), "ps_find_peaks d2h");
   PS_CUDA(cudaStreamSynchronize(st), "Error from device_find_peaks;");
+  ws->needed = count;
   if (count > ws->cap || count > max_out) {
     set_error("ps_find_peaks: more peaks above threshold than the workspace/output can hold");
     return PS_EOVERFLOW;
@@ -422,6 +424,8 @@ int ps_find_peaks(int n, int start, const float* d_dat, float thresh, int* h_idx
   }
   return (int)count;
 }
+
+size_t ps_peak_workspace_needed(const ps_peak_workspace* ws) { return ws ? ws->needed : 0; }
 
 int ps_median_scrunch5(const float* d_in, size_t count, float* d_out, void* stream) {
   if (!count) return PS_OK;

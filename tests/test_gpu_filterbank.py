@@ -53,6 +53,48 @@ def test_dedisperse_random_filterbanks(lib, oracle, nbits, nchans):
     assert got[0].std() > 0
 
 
+@pytest.mark.parametrize("nbits,nchans,budget", [(2, 64, 3 << 20), (8, 16, 2 << 20), (1, 32, 1200000), (4, 48, 3 << 20)])
+def test_dedisperse_in_time_gulps_equals_one_gulp(lib, oracle, nbits, nchans, budget):
+    """ps_dedisperse_on with a small device-memory budget processes the observation in several time
+    gulps (gulp + max_delay samples of input each): same bytes as the single-gulp call and as the oracle,
+    for gulp lengths that do not divide the observation."""
+    rng = np.random.default_rng(nbits * 77 + nchans)
+    nsamps = 60000
+    raw = rng.integers(0, 256, nsamps * nchans * nbits // 8, dtype=np.uint8)
+    hdr = dict(nbits=nbits, nchans=nchans, nsamples=nsamps, tsamp=64e-6, fch1=1510.0, foff=-300.0 / nchans)
+    dms = np.array([0.0, 3.3, 17.0, 55.5, 120.0], np.float32)
+    kill = (rng.random(nchans) > 0.2).astype(np.int32)
+    one = dedisperse(lib, raw, hdr, dms, killmask=kill)
+    md = hdr["nsamples"] - one.shape[1]
+    out = np.zeros_like(one)
+    n0 = lib.ps_launch_count()
+    pb.check(lib.ps_dedisperse_on(-1, budget, raw.ctypes.data, nsamps, nchans, nbits, hdr["tsamp"], hdr["fch1"], hdr["foff"],
+                                  dms.ctypes.data, len(dms), kill.ctypes.data, out.ctypes.data, one.shape[1]))
+    assert lib.ps_launch_count() - n0 >= 6          # at least three gulps of two kernels
+    assert np.array_equal(out, one)
+    want, _ = oracle.dedisperse(raw, hdr, dms, killmask=kill)
+    assert np.array_equal(out, want) and md > 0
+    # a budget that cannot hold one 64-sample gulp is an error, not a crash
+    assert lib.ps_dedisperse_on(-1, 4096, raw.ctypes.data, nsamps, nchans, nbits, hdr["tsamp"], hdr["fch1"], hdr["foff"],
+                                dms.ctypes.data, len(dms), kill.ctypes.data, out.ctypes.data, one.shape[1]) == -2
+    assert b"device memory" in lib.ps_last_error()
+
+
+def test_dedisperse_rejects_negative_delays(lib):
+    """An ascending band (foff > 0), a negative DM or an unsorted DM list would need samples before the
+    start of the data (delays are unsigned sample counts): refused explicitly."""
+    x = np.zeros(4096 * 8, np.uint8)
+    out = np.zeros(4096 * 2, np.uint8)
+    d = np.array([0.0, 50.0], np.float32)
+    assert lib.ps_dedisperse(x.ctypes.data, 4096, 8, 8, 64e-6, 1200.0, +10.0, d.ctypes.data, 2, None, out.ctypes.data, 4096) == -2
+    assert b"negative delay" in lib.ps_last_error()
+    d = np.array([-5.0, 50.0], np.float32)
+    assert lib.ps_dedisperse(x.ctypes.data, 4096, 8, 8, 64e-6, 1500.0, -10.0, d.ctypes.data, 2, None, out.ctypes.data, 4096) == -2
+    d = np.array([50.0, 10.0], np.float32)
+    assert lib.ps_dedisperse(x.ctypes.data, 4096, 8, 8, 64e-6, 1500.0, -10.0, d.ctypes.data, 2, None, out.ctypes.data, 4096) == -2
+    assert b"ascend" in lib.ps_last_error()
+
+
 def test_dedisperse_rejects_bad_arguments(lib):
     x = np.zeros(64, np.uint8)
     d = np.zeros(1, np.float32)

@@ -171,7 +171,17 @@ def test_find_peaks_overflow_is_an_error(lib):
     check(lib.ps_peak_workspace_create(100, C.byref(ws)))
     hi = np.zeros(100, np.int32)
     hs = np.zeros(100, np.float32)
-    assert lib.ps_find_peaks(5000, 0, ptr(x), 0.5, ptr(hi), ptr(hs), 100, ws, None) == -3
+    assert lib.ps_find_peaks(5000, 10, ptr(x), 0.5, ptr(hi), ptr(hs), 100, ws, None) == -3
+    # ... and the workspace says how many there were, so the caller can grow and search again
+    # (PeakFinder::find_candidates of the mirror does: 1.5x the count, like the fused path's peak list)
+    need = lib.ps_peak_workspace_needed(ws)
+    assert need == 4990
+    lib.ps_peak_workspace_destroy(ws)
+    check(lib.ps_peak_workspace_create(need + need // 2, C.byref(ws)))
+    hi = np.zeros(need + need // 2, np.int32)
+    hs = np.zeros(need + need // 2, np.float32)
+    assert lib.ps_find_peaks(5000, 10, ptr(x), 0.5, ptr(hi), ptr(hs), len(hi), ws, None) == need
+    assert np.array_equal(hi[:need], np.arange(10, 5000))
     lib.ps_peak_workspace_destroy(ws)
 
 
