@@ -1,6 +1,6 @@
 """Per-warp phase cycle counters of the warp-specialised pass 1 (build with `make EXTRA=-DPS_PROF`)."""
 import sys, os, ctypes as C
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import peasoup_b200 as pb
 from peasoup_b200.host import make_search_params
