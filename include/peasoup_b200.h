@@ -101,6 +101,8 @@ int ps_running_median(const float* d_pspec, unsigned nbins, double bin_width, fl
  *  - all calls on a device share the one array: calls whose kernels may overlap on the GPU
  *    (different streams without ordering between them) race -- serialise them.  Nothing has to
  *    be cleared between calls: every level is rewritten before it is read;
+ *  - the array used is that of the CURRENT device: d_pspec and d_median must live on it (the call
+ *    does not check where they live);
  *  - results are identical to ps_running_median on the same input. */
 #define PS_RUNNING_MEDIAN_NOALLOC_MAX_BINS 4194305u
 int ps_running_median_noalloc(const float* d_pspec, unsigned nbins, double bin_width,
