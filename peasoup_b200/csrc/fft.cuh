@@ -109,6 +109,10 @@ struct LoadResampled {
   // run in memory.  A warp's load then touches 4 runs of 64 bytes instead of 8 scattered sectors.
   const float2* D;
   AccelFacts afs;
+  // the kernel's own (grid-constant) parameter copy of afs.v: indexed per work item straight from the
+  // parameter bank -- indexing the by-value member would make the compiler keep the whole table in
+  // local memory (328-byte stack frame, one local load per work item on the critical path)
+  const double* afp = nullptr;
   double size;
   float max_shift;  // host bound on |i*af*(i-N)| over the series, all batch items
   float max_step;   // host bound on |shift(i+1) - shift(i)|
@@ -117,8 +121,9 @@ struct LoadResampled {
   float af32, fsize, thr;
   int n2, c0;
   unsigned col_mask, wrap;
+  __device__ __forceinline__ void bind(const LoadResampled& param) { afp = param.afs.v; }
   __device__ __forceinline__ void begin(int b, int first, int n) {
-    af = afs.v[b];
+    af = afp[b];
     af32 = (float)af;
     fsize = (float)size;
     // float32 evaluation error of the shift: fi and fi - N are exact (even integers up to 2^25), so three roundings (the
@@ -306,6 +311,16 @@ struct loads_whole_column { static constexpr bool value = false; };
 template <class L>
 struct loads_whole_column<L, decltype((void)L::kWholeColumn)> { static constexpr bool value = true; };
 
+// loaders that index tables of their kernel parameter bind to the grid-constant copy (LoadResampled)
+template <class L, class = void>
+struct binds_param { static constexpr bool value = false; };
+template <class L>
+struct binds_param<L, decltype((void)&L::afp)> { static constexpr bool value = true; };
+template <class Loader>
+__device__ __forceinline__ void bind_loader(Loader& ld, const Loader& param) {
+  if constexpr (binds_param<Loader>::value) ld.bind(param);
+}
+
 template <class C, class Loader>
 __device__ __forceinline__ void load_operands(const Loader& ld, cf* v) {
   const int t = threadIdx.x, f = t % C::F, u = t / C::F;
@@ -319,8 +334,11 @@ __device__ __forceinline__ void load_operands(const Loader& ld, cf* v) {
 
 // grid-stride over (batch item, tile); items are independent transforms with their own Yt slice
 template <int R3, bool INV, class Loader>
-__global__ void __launch_bounds__(512, 1) fft_pass1_kernel(Loader ld, cf* Yt, FftTables t, int n1, int n2, int nbatch, int tw2) {
+__global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant__ Loader ldp, cf* Yt, FftTables t, int n1, int n2,
+                                                           int nbatch, int tw2) {
   using C = psfft::CtaFft<R3, INV>;
+  Loader ld = ldp;
+  bind_loader(ld, ldp);
   extern __shared__ float smem[];
   const int ntiles = n2 / C::F;
   const int nwork = ntiles * nbatch;

@@ -298,6 +298,7 @@ __global__ void __launch_bounds__(256) ramp_pairs_kernel(float2* __restrict__ D,
 }
 __global__ void __launch_bounds__(256) loader_dump_kernel(LoadResampled ld, float2* __restrict__ out, unsigned M, int n2,
                                                           unsigned* __restrict__ exact) {
+  ld.bind(ld);  // (a by-value parameter: its table sits in this thread's local memory, fine for a diagnostic)
   ld.begin(0, 0, n2);
   for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < M; e += gridDim.x * blockDim.x) {
     const cf v = ld.at(2u * e);

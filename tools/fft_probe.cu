@@ -73,6 +73,7 @@ float run(const char* name, const cf* Yt, Storer st, FftTables t, int n1, int n2
 
 template <int MODE, class Storer>
 __global__ void __launch_bounds__(512, 1) probe1_kernel(LoadResampled ld, Storer st0, cf* Yt, FftTables t, int n1, int n2, int nbatch, int tw2) {
+  ld.bind(ld);
   using C = psfft::CtaFft<8, false>;
   extern __shared__ float smem[];
   const int ntiles = n2 / C::F, nwork = ntiles * nbatch;
