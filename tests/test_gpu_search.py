@@ -269,6 +269,24 @@ def test_pipeline_vs_reference_cuda_build(lib, oracle, ref, tmp_path):
     compare_candidates(got, want, cfg)
 
 
+@pytest.mark.parametrize("nharm", [0, 1, 2, 3, 5])
+def test_pipeline_other_fold_counts_vs_reference_cuda_build(lib, oracle, ref, nharm):
+    """-n 0 .. 5 (no harmonic sums ... 32 harmonics) through the whole loop against the unmodified
+    reference build: 1-3 folds take the TMA-staged harmonic kernel with fewer ranges, 5 folds the
+    gather kernel, 0 folds thresholds the fundamental spectrum alone."""
+    size, nsamps, tsamp = 1 << 19, (1 << 19) + 100, 64e-6
+    ndm = 2
+    trials = make_trials(ndm, nsamps, size, tsamp=tsamp, a_inj=15.0, amp=7.0, seed=nharm)
+    dms = np.array([3.0, 9.0], np.float32)
+    accs = np.array([0.0, 15.0, -15.0], np.float32)
+    cfg = oracle.SearchConfig(size, tsamp, nharmonics=nharm)
+    want, _ = ref_search(ref, trials, dms, accs, size, nsamps, tsamp, nharm=nharm)
+    got, done = pb.pipeline_search(trials, dms, pipeline_params(size, nsamps, tsamp, nharm=nharm), accs=accs)
+    assert done == ndm * len(accs) and len(want) > 0
+    compare_candidates(got, want, cfg)
+    assert int(got["nh"].max()) <= nharm
+
+
 def test_tutorial_vs_reference_cuda_build(lib, oracle, ref, tutorial_trials):
     trials, ov = tutorial_trials
     size, tsamp = 1 << 17, 0.00032
