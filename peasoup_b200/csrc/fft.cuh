@@ -423,6 +423,8 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
   }
   __syncthreads();
   unsigned parity = 0;
+  // the thread's two twiddle bases do not depend on the work item (80 registers: room to keep them)
+  const cf wA = C::twiddleA(threadIdx.x, t.W4096), wB = R3 > 1 ? C::twiddleB(threadIdx.x, t.W4096) : psfft::mk(1.f, 0.f);
   for (; slot < nwork; slot += gridDim.x) {
     const int work = reverse ? nwork - 1 - slot : slot;
     const int b = work / ntiles, tile = work - b * ntiles;
@@ -432,7 +434,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
     cf v[16];
 #pragma unroll
     for (int a = 0; a < 16; a++) v[a] = stage[a * C::THREADS + threadIdx.x];
-    C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
+    C::phaseA_regs_w(threadIdx.x, smem, wA, v);
     __syncthreads();  // E1 complete; every thread has taken its operands out of the staging buffer
     const int next_slot = slot + gridDim.x;
     if (threadIdx.x == 0 && next_slot < nwork) {
@@ -441,7 +443,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass2_kernel(const cf* Yt, Storer 
       mbar_expect_tx(&bar, kTileBytes);
       bulk_g2s(stage, Yt + (size_t)next * tile_elems, kTileBytes, &bar);
     }
-    C::phaseB(threadIdx.x, smem, t.W4096, st);
+    C::phaseB_w(threadIdx.x, smem, wB, st);
     __syncthreads();
     C::phaseC(threadIdx.x, smem, st);
   }

@@ -199,10 +199,18 @@ struct CtaFft {
     phaseA_write(t, s, v);
   }
   PS_HD static void phaseA_compute(int t, const cf* W4096, cf* v) {
-    const int u = t / F;
     dft16<INV>(v);
-    cf w1 = ldg_cf(&W4096[u * (4096 / N)]);
-    twiddle_powers16(v, dirw<INV>(w1));
+    twiddle_powers16(v, dirw<INV>(twiddleA(t, W4096)));
+  }
+  // The two twiddle bases of a thread depend on its position only, not on the work item: a kernel
+  // with registers to spare loads them once (twiddleA / twiddleB) and passes them in (phaseA_regs_w,
+  // phaseB_w).
+  PS_HD static cf twiddleA(int t, const cf* W4096) { return ldg_cf(&W4096[(t / F) * (4096 / N)]); }         // W_n^u
+  PS_HD static cf twiddleB(int t, const cf* W4096) { return ldg_cf(&W4096[((t / F) % R3) * (256 / R3)]); }  // W_(16*R3)^c
+  PS_HD static void phaseA_regs_w(int t, float* s, cf wA, cf* v) {
+    dft16<INV>(v);
+    twiddle_powers16(v, dirw<INV>(wA));
+    phaseA_write(t, s, v);
   }
   PS_HD static void phaseA_write(int t, float* s, const cf* v) {
     const int f = t % F, u = t / F;
@@ -213,6 +221,10 @@ struct CtaFft {
 
   template <class Storer>
   PS_HD static void phaseB(int t, float* s, const cf* W4096, const Storer& st) {
+    phaseB_w(t, s, R3 == 1 ? mk(1.f, 0.f) : twiddleB(t, W4096), st);
+  }
+  template <class Storer>
+  PS_HD static void phaseB_w(int t, float* s, cf wB, const Storer& st) {
     const int f = t % F, u = t / F;
     const int ka = u / R3, c = u % R3;
     const cf* e1 = reinterpret_cast<const cf*>(s);
@@ -224,8 +236,7 @@ struct CtaFft {
       st.template store<16>(f, ka, 16, v);
       return;
     }
-    cf w1 = ldg_cf(&W4096[c * (256 / R3)]);  // W_(16*R3)^c
-    twiddle_powers16(v, dirw<INV>(w1));
+    twiddle_powers16(v, dirw<INV>(wB));
     cf* e2 = reinterpret_cast<cf*>(s) + E1_WORDS;
 #pragma unroll
     for (int kb = 0; kb < 16; kb++) e2[((ka + 16 * kb) * (R3 + 1) + c) * F + f] = v[kb];
