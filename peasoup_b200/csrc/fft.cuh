@@ -351,12 +351,13 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant
   // so the input needs no L2 residency across batch items
   ld.begin(work % nbatch, (work / nbatch) * C::F, n2);
   load_operands<C>(ld, v);
+  const cf wA = C::twiddleA(threadIdx.x, t.W4096), wB = R3 > 1 ? C::twiddleB(threadIdx.x, t.W4096) : psfft::mk(1.f, 0.f);
   for (; work < nwork; work += gridDim.x) {
     const int tile = work / nbatch, b = work - tile * nbatch;
     StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F, n2, tw2};
-    C::phaseA_regs(threadIdx.x, smem, t.W4096, v);
+    C::phaseA_regs_w(threadIdx.x, smem, wA, v);
     __syncthreads();
-    C::phaseB(threadIdx.x, smem, t.W4096, st);
+    C::phaseB_w(threadIdx.x, smem, wB, st);
     // (issued before the barrier: the loads are in flight while the CTA waits for its slowest warp)
     const int next = work + gridDim.x;
     if (next < nwork) {
