@@ -126,10 +126,14 @@ struct LoadResampled {
     af = afp[b];
     af32 = (float)af;
     fsize = (float)size;
-    // float32 evaluation error of the shift: fi and fi - N are exact (even integers up to 2^25), so three roundings (the
-    // product, af32 = float(af), the final product) give <= 1.8e-7 |shift| -- 3e-7 with margin.  A
-    // shift estimate this far from a half-integer fixes the rounding of both samples of a pair.
-    thr = 0.5f - (1e-3f + 3e-7f * max_shift + max_step);
+    // float32 evaluation error of the shift: fi and fi - N are exact (even integers up to 2^25), so three
+    // roundings (the product, af32 = float(af), the final product) give <= 3 * 2^-24 = 1.79e-7 |shift|
+    // (2e-7 used); the second sample of the pair adds at most max_step; the reference's own FP64
+    // evaluation of i + i*af*(i-N) is good to (|shift| + i) * 2^-52 < 1e-8 samples, and this float
+    // expression to ~3e-8: 1e-5 covers both.  A shift estimate this far from a half-integer fixes the
+    // rounding of both samples of a pair; the index maps are pinned bit for bit by
+    // test_product_resample_index_map_bit_exact.
+    thr = 0.5f - (1e-5f + 2e-7f * max_shift + max_step);
     c0 = first;
     n2 = n;
     col_mask = (1u << lg_n2) - 1u;
