@@ -107,7 +107,11 @@ struct LoadResampled {
   // The whitened series is kept TRANSPOSED as complex pairs: pair e = (x[2e], x[2e+1]) of the natural
   // series lives at D[(e % n2) * n1 + e / n2], so the column a pass-1 tile transforms is a contiguous
   // run in memory.  A warp's load then touches 4 runs of 64 bytes instead of 8 scattered sectors.
+  // The loader reads the TWO-PHASE form D4[same index] = (x[2e], x[2e+1] | x[2e+1], x[2e+2]): the pair
+  // for an even shift in its first half, for an odd shift in its second half, so either is ONE
+  // aligned 8-byte load at index 2*p + parity -- no second address, no divergence on the parity.
   const float2* D;
+  const float4* D4;
   AccelFacts afs;
   // the kernel's own (grid-constant) parameter copy of afs.v: indexed per work item straight from the
   // parameter bank -- indexing the by-value member would make the compiler keep the whole table in
@@ -120,7 +124,7 @@ struct LoadResampled {
   double af;
   float af32, fsize, thr;
   int n2, c0;
-  unsigned col_mask, wrap;
+  unsigned col_mask;
   __device__ __forceinline__ void bind(const LoadResampled& param) { afp = param.afs.v; }
   __device__ __forceinline__ void begin(int b, int first, int n) {
     af = afp[b];
@@ -137,7 +141,6 @@ struct LoadResampled {
     c0 = first;
     n2 = n;
     col_mask = (1u << lg_n2) - 1u;
-    wrap = 1u - col_mask * (unsigned)n1;
   }
   // pair e of the natural series -> its place in the transposed layout (at most 2^24 pairs: 32-bit math)
   __device__ __forceinline__ unsigned pair_index(unsigned e) const { return (e & col_mask) * (unsigned)n1 + (e >> lg_n2); }
@@ -150,18 +153,11 @@ struct LoadResampled {
     const float g = (fi * (fi - fsize)) * af32;         // shift estimate
     const float tm = g + 12582912.f;                    // 1.5*2^23: rounds g to an integer (ties to even)
     const float r = tm - 12582912.f;
-    const float* Df = reinterpret_cast<const float*>(D);
     if (fabsf(g - r) < thr) {  // samples i0, i0 + 1
       const unsigned i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
       const unsigned e = i0 >> 1;
-      const unsigned p = pair_index(e);
-      if ((i0 & 1u) == 0) {  // both samples in one pair: one 8-byte load
-        float2 v = __ldg(&D[p]);
-        return psfft::mk(v.x, v.y);
-      }
-      // pair e + 1 sits one column on (n1 pairs), or at the top of the next row after the last column
-      const unsigned p2 = p + (((e & col_mask) == col_mask) ? wrap : (unsigned)n1);
-      return psfft::mk(__ldg(&Df[2u * p + 1u]), __ldg(&Df[2u * p2]));
+      const float2 v = __ldg(reinterpret_cast<const float2*>(D4) + (2u * pair_index(e) + (i0 & 1u)));
+      return psfft::mk(v.x, v.y);
     }
     // the reference's FP64 expression (kernels.cu:314-317), each sample on its own
     return exact(i);
