@@ -49,7 +49,7 @@ class DMDispenser {  // pipeline_multi.cu:33-81 (progress bar omitted)
   }
 };
 
-// Device-side state of one worker: two DM trials in flight (search handle, stream, staging).
+// Device-side state of one worker: up to kMaxSlots DM trials in flight (search handle, stream, staging).
 // Creating it costs ~40 cudaMalloc calls and table uploads, so a long-lived pipeline keeps it
 // across calls (ps_pipeline_open); a one-shot Worker builds its own.
 class WorkerSlots {
@@ -65,6 +65,14 @@ class WorkerSlots {
   };
   enum { kMaxSlots = 4 };
   Slot slots[kMaxSlots];
+  // recorded behind every slot's device work: the next slot's device work waits for it.  The kernels
+  // are persistent over the whole GPU with a static work partition; kernels of two DM trials side by
+  // side (the other trial's small whitening kernels taking SMs for a few microseconds at a time)
+  // delay single CTAs and with them the whole kernel: measured 5.59 ms per DM trial with two free-running
+  // slots against 5.16 ms = whitening + chain with one.  The slots still overlap the host's share.
+  cudaEvent_t chain_done = 0;
+  bool chain_recorded = false;
+  bool serial_chains = true;
   int nslots;
   int device;
   ps_search_params prm;
@@ -72,13 +80,15 @@ class WorkerSlots {
 
   WorkerSlots(int device, const ps_search_params& prm, const std::vector<float>& zf, const std::vector<float>& zw)
       : device(device), prm(prm), ncopy(std::min(prm.nsamps, prm.size)) {
-    // DM trials in flight per worker: the next trial's copy, whitening and kernels are queued while
-    // the host distills the previous one.  With 32 acceleration trials per launch two are enough
-    // (measured trials/s at 1/2/3/4: 11.7k / 16.1k / 15.8k / 15.6k -- more slots only compete for
-    // the L2); PS_SLOTS overrides.
-    nslots = 2;
+    // DM trials in flight per worker: the next trial's copy is queued and its kernels wait behind the
+    // previous trial's (chain_done) while the host distills earlier ones.  With the kernels serialised,
+    // ms per DM trial at 2/3/4 slots, one box: 5.43 / 5.35 / 5.37 over 64 DM trials, 5.47 / 5.18 over
+    // 16 (the third slot hides the host's share of the first and last trials); PS_SLOTS overrides.
+    nslots = 3;
     if (const char* e = getenv("PS_SLOTS")) nslots = std::max(1, std::min((int)kMaxSlots, atoi(e)));
+    if (const char* e = getenv("PS_SERIAL")) serial_chains = atoi(e) != 0;
     ErrorChecker::check_cuda_error(cudaSetDevice(device), "cudaSetDevice");
+    ErrorChecker::check_cuda_error(cudaEventCreateWithFlags(&chain_done, cudaEventDisableTiming), "cudaEventCreate");
     const unsigned cap = prm.max_peaks ? prm.max_peaks : (1u << 20);
     try {
       for (int i = 0; i < nslots; i++) {
@@ -110,6 +120,8 @@ class WorkerSlots {
       if (slots[i].stream) cudaStreamDestroy(slots[i].stream);
       slots[i] = Slot();
     }
+    if (chain_done) cudaEventDestroy(chain_done);
+    chain_done = 0;
   }
 };
 
@@ -277,9 +289,18 @@ class Worker {  // pipeline_multi.cu:83-254
         s.acc_list = *fixed_accs;
       else
         acc_plan.generate_accel_list(s.dm, s.acc_list);
+      // the KERNELS of this trial start when the previous trial's are done (see chain_done): the slots
+      // overlap the host's share (peak fetch, clustering, distillation, submission) and the copy engine's
+      // (the trial's H2D above) with the other slot's kernels, not kernels with kernels
+      if (ws->serial_chains && ws->chain_recorded)
+        ErrorChecker::check_cuda_error(cudaStreamWaitEvent(s.stream, ws->chain_done, 0), "cudaStreamWaitEvent");
       ErrorChecker::check(ps_search_reset_peaks(s.search, s.stream));
       ErrorChecker::check(ps_search_whiten(s.search, s.d_trial, 0, 0, s.stream));
       ErrorChecker::check(ps_search_accel_batch(s.search, &s.acc_list[0], (int)s.acc_list.size(), 0, s.stream));
+      if (ws->serial_chains) {
+        ErrorChecker::check_cuda_error(cudaEventRecord(ws->chain_done, s.stream), "cudaEventRecord");
+        ws->chain_recorded = true;
+      }
       t_submit += secs(t0, clk::now());
       return true;
     };

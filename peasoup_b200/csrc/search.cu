@@ -20,7 +20,16 @@
 namespace ps {
 
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
-constexpr int kAccelBatch = 32;  // acceleration trials per launch: amortises kernel ramp-up/drain and the 148-SM wave tail (measured us/trial: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7)
+// acceleration trials per launch: amortises kernel ramp-up/drain and the 148-SM wave tail (measured chain
+// us/trial at 2^23 -- r1: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7; r2: 26: 49.7, 34: 49.5, 51: 49.1).  Up to 64,
+// fewer for long transforms: the inter-pass buffer, the packed spectra and the spectra of a launch
+// (20 bytes per sample and trial) are kept under kBatchBytes per handle.
+constexpr int kAccelBatch = 64;
+constexpr size_t kBatchBytes = (size_t)12 << 30;
+static int accel_batch_for(unsigned size) {
+  const size_t per_trial = (size_t)20 * size;
+  return (int)std::max<size_t>(8, std::min<size_t>(kAccelBatch, kBatchBytes / per_trial));
+}
 void plan_destroy(ps_fft_plan_t* p);
 
 struct LevelRanges {
@@ -442,7 +451,8 @@ struct Search {
   unsigned needed = 0;  // record count of the last fetch (ps_search_peaks_needed)
   LevelRanges ranges;
   LevelScales scales;
-  float* d_pbatch = nullptr;   // kBatch spectra (stride pstride floats)
+  int batch = 0;               // acceleration trials per launch (accel_batch_for(size))
+  float* d_pbatch = nullptr;   // `batch` spectra (stride pstride floats)
   size_t pstride = 0;
   const float* last_spectrum = nullptr;
   float bin_width_f = 0.f;   // float bin_width = 1.0/tobs   (pipeline_multi.cu:118-119)
@@ -507,7 +517,8 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   s->prm = *p;
   if (s->prm.boundary_5_freq <= 0) s->prm.boundary_5_freq = 0.05f;
   if (s->prm.boundary_25_freq <= 0) s->prm.boundary_25_freq = 0.5f;
-  int rc = plan_create(p->size, &s->plan, kAccelBatch);
+  s->batch = accel_batch_for(p->size);
+  int rc = plan_create(p->size, &s->plan, s->batch);
   if (rc) {
     delete s;
     return rc;
@@ -547,7 +558,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (e == cudaSuccess) e = cudaMemset(s->d_stats, 0, sizeof(float) * 4);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_peaks, sizeof(ps_raw_peak) * (size_t)s->cap);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_count, sizeof(unsigned));
-  if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * kAccelBatch);
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * s->batch);
   if (e == cudaSuccess) e = cudaMemset(s->d_count, 0, sizeof(unsigned));
   if (e != cudaSuccess) {
     free_search(s);
@@ -689,7 +700,8 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   const ps_fft_plan_t* p = s->plan;
   unsigned size = s->prm.size;
   int rc;
-  static const int env_batch = getenv("PS_BATCH") ? std::max(1, std::min(kAccelBatch, atoi(getenv("PS_BATCH")))) : kAccelBatch;
+  static const int env_batch_cap = getenv("PS_BATCH") ? std::max(1, atoi(getenv("PS_BATCH"))) : kAccelBatch;
+  const int env_batch = std::min(env_batch_cap, s->batch);
 #ifdef PS_PROFILING  // profiling builds only (make EXTRA=-DPS_PROFILING): the shipped library has no such switch
   static const int env_skip = getenv("PS_SKIP") ? atoi(getenv("PS_SKIP")) : 0;
 #else
