@@ -107,11 +107,14 @@ struct LoadResampled {
   // The whitened series is kept TRANSPOSED as complex pairs: pair e = (x[2e], x[2e+1]) of the natural
   // series lives at D[(e % n2) * n1 + e / n2], so the column a pass-1 tile transforms is a contiguous
   // run in memory.  A warp's load then touches 4 runs of 64 bytes instead of 8 scattered sectors.
-  // The loader reads the TWO-PHASE form D4[same index] = (x[2e], x[2e+1] | x[2e+1], x[2e+2]): the pair
-  // for an even shift in its first half, for an odd shift in its second half, so either is ONE
-  // aligned 8-byte load at index 2*p + parity -- no second address, no divergence on the parity.
+  // The loader reads the TWO-PHASE form of that layout: plane 2c holds column c as it is (the pair for an
+  // even shift), plane 2c + 1 the same column one sample on, (x[2e+1], x[2e+2]) (the pair for an odd
+  // shift): Dph[((2c + parity) * n1) + row].  The low lg(n2) + 1 bits of the first sample's index i0 are
+  // exactly 2c + parity and the rest is the row, so either pair is ONE aligned 8-byte load behind a
+  // mask, a shift and a multiply-add -- no second address, no divergence on the parity -- and the 8
+  // rows x 4 columns a warp reads (nearly always of one parity) are 4 runs of 64 bytes.
   const float2* D;
-  const float4* D4;
+  const float2* Dph;
   AccelFacts afs;
   // the kernel's own (grid-constant) parameter copy of afs.v: indexed per work item straight from the
   // parameter bank -- indexing the by-value member would make the compiler keep the whole table in
@@ -124,7 +127,7 @@ struct LoadResampled {
   double af;
   float af32, fsize, thr;
   int n2, c0;
-  unsigned col_mask;
+  unsigned col_mask, plane_mask, plane_shift;
   __device__ __forceinline__ void bind(const LoadResampled& param) { afp = param.afs.v; }
   __device__ __forceinline__ void begin(int b, int first, int n) {
     af = afp[b];
@@ -141,6 +144,8 @@ struct LoadResampled {
     c0 = first;
     n2 = n;
     col_mask = (1u << lg_n2) - 1u;
+    plane_mask = (2u << lg_n2) - 1u;
+    plane_shift = (unsigned)lg_n2 + 1u;
   }
   // pair e of the natural series -> its place in the transposed layout (at most 2^24 pairs: 32-bit math)
   __device__ __forceinline__ unsigned pair_index(unsigned e) const { return (e & col_mask) * (unsigned)n1 + (e >> lg_n2); }
@@ -155,8 +160,7 @@ struct LoadResampled {
     const float r = tm - 12582912.f;
     if (fabsf(g - r) < thr) {  // samples i0, i0 + 1
       const unsigned i0 = i + (unsigned)(__float_as_int(tm) - 0x4B400000);
-      const unsigned e = i0 >> 1;
-      const float2 v = __ldg(reinterpret_cast<const float2*>(D4) + (2u * pair_index(e) + (i0 & 1u)));
+      const float2 v = __ldg(Dph + ((i0 & plane_mask) * (unsigned)n1 + (i0 >> plane_shift)));
       return psfft::mk(v.x, v.y);
     }
     // the reference's FP64 expression (kernels.cu:314-317), each sample on its own
@@ -260,14 +264,29 @@ struct StorePass1 {
     const cf base = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k0));
     cf pw[R > 1 ? R : 2];
     psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride)));
-    float2* out = reinterpret_cast<float2*>(Yt) + (size_t)j2 * tw;
-    const unsigned twm = (unsigned)tw - 1u;  // tw is a power of two
+    // tw (rows per pass-2 tile, a power of two <= 32) divides the stride of every call but the 16-point one:
+    // the run position k % tw is then the same for all j and the R stores are one base address plus
+    // multiples of a constant -- 32-bit element offsets inside this item's slice (M <= 2^24 elements)
+    // instead of a 64-bit index product per store.
+    const unsigned twm = ((unsigned)tw - 1u) & 31u;
+    float2* out = reinterpret_cast<float2*>(Yt);
+    if (((unsigned)stride & twm) == 0u) {
+      const unsigned o0 = j2 * (unsigned)tw + ((unsigned)k0 & ~twm) * (unsigned)n2 + ((unsigned)k0 & twm);
+      const unsigned step = (unsigned)stride * (unsigned)n2;
+#pragma unroll
+      for (int j = 0; j < R; j++) {
+        const cf o = psfft::cmul(v[j], pw[j]);
+        // streaming store: the inter-pass data is read once, much later -- it should not displace the
+        // whitened series (re-read by every acceleration trial) from the L2
+        __stcs(&out[o0 + step * (unsigned)j], make_float2(o.x, o.y));
+      }
+      return;
+    }
+    out += (size_t)j2 * tw;
 #pragma unroll
     for (int j = 0; j < R; j++) {
-      cf o = psfft::cmul(v[j], pw[j]);
+      const cf o = psfft::cmul(v[j], pw[j]);
       const unsigned k = (unsigned)(k0 + stride * j);
-      // streaming store: the inter-pass data is read once, much later -- it should not displace the
-      // whitened series (re-read by every acceleration trial) from the L2
       __stcs(&out[(size_t)(k & ~twm) * n2 + (k & twm)], make_float2(o.x, o.y));
     }
   }
@@ -352,16 +371,23 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant
   ld.begin(work % nbatch, (work / nbatch) * C::F, n2);
   load_operands<C>(ld, v);
   const cf wA = C::twiddleA(threadIdx.x, t.W4096), wB = R3 > 1 ? C::twiddleB(threadIdx.x, t.W4096) : psfft::mk(1.f, 0.f);
+  // (tile, b) of the work item whose operands are in v, stepped by the grid size without a division
+  const int dtile = (int)gridDim.x / nbatch, db = (int)gridDim.x - dtile * nbatch;
+  int tile = work / nbatch, b = work - tile * nbatch;
   for (; work < nwork; work += gridDim.x) {
-    const int tile = work / nbatch, b = work - tile * nbatch;
     StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F, n2, tw2};
     C::phaseA_regs_w(threadIdx.x, smem, wA, v);
     __syncthreads();
     C::phaseB_w(threadIdx.x, smem, wB, st);
     // (issued before the barrier: the loads are in flight while the CTA waits for its slowest warp)
-    const int next = work + gridDim.x;
-    if (next < nwork) {
-      ld.begin(next % nbatch, (next / nbatch) * C::F, n2);
+    tile += dtile;
+    b += db;
+    if (b >= nbatch) {
+      b -= nbatch;
+      tile++;
+    }
+    if (work + (int)gridDim.x < nwork) {
+      ld.begin(b, tile * C::F, n2);
       load_operands<C>(ld, v);
     }
     __syncthreads();

@@ -299,9 +299,11 @@ __global__ void __launch_bounds__(256) untranspose_pairs_kernel(const float2* __
     out[e] = D[(size_t)(e & ((1u << lg_n2) - 1u)) * n1 + (e >> lg_n2)];
 }
 
-// D4[q] = (x[2e], x[2e+1], x[2e+1], x[2e+2]) from D[q] and the next pair's first sample: pair e sits at q = (e % n2) * n1 + e / n2, pair e+1 one column on
-// (n1 words), or in row+1 of column 0 after the last column; the very last pair has no successor.
-__global__ void __launch_bounds__(256) quad_pairs_kernel(const float2* __restrict__ D, float4* __restrict__ D4, unsigned M, int n1) {
+// Two-phase form of the transposed series (LoadResampled): pair e = (x[2e], x[2e+1]) sits at q = c * n1 + row of D
+// (c = e % n2, row = e / n2); plane 2c of Dph is column c itself, plane 2c + 1 the pairs one sample on,
+// (x[2e+1], x[2e+2]).  Pair e+1 is one column on (n1 words), or in row+1 of column 0 after the last column;
+// the very last pair has no successor.
+__global__ void __launch_bounds__(256) phase_planes_kernel(const float2* __restrict__ D, float2* __restrict__ Dph, unsigned M, int n1) {
   for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < M; q += gridDim.x * blockDim.x) {
     const unsigned row = q % (unsigned)n1;
     const bool last_col = q + (unsigned)n1 >= M;
@@ -309,7 +311,9 @@ __global__ void __launch_bounds__(256) quad_pairs_kernel(const float2* __restric
     float2 b = make_float2(0.f, 0.f);
     if (!(last_col && row + 1u >= (unsigned)n1)) b = D[nxt];
     const float2 a = D[q];
-    D4[q] = make_float4(a.x, a.y, a.y, b.x);
+    const size_t o = (size_t)q + (q - row);  // 2 c n1 + row
+    Dph[o] = a;
+    Dph[o + (unsigned)n1] = make_float2(a.y, b.x);
   }
 }
 
@@ -432,7 +436,7 @@ struct Search {
   unsigned nbins = 0;
   float* d_tim = nullptr;      // whitened series as size/2 complex pairs, TRANSPOSED (see LoadResampled)
   float* d_tim_nat = nullptr;  // natural-order copy, made on request (ps_search_whitened_series)
-  float4* d_tim4 = nullptr;    // two-phase form read by the resampling loader: [same index] = (x[2e], x[2e+1] | x[2e+1], x[2e+2])
+  float2* d_tim_ph = nullptr;  // two-phase form read by the resampling loader (phase_planes_kernel): 2 * size/2 pairs
   int lg_n2 = 0;    // log2(pair columns) of the transposed whitened series
   int col_len = 0;  // pairs per column
   float2* d_X = nullptr;       // nbins complex
@@ -462,7 +466,7 @@ struct Search {
 static void free_search(Search* s) {
   if (!s) return;
   plan_destroy(s->plan);
-  cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_tim4); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
+  cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_tim_ph); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
   cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch);
   delete s;
@@ -546,7 +550,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   }
   size_t nb = s->nbins;
   cudaError_t e = cudaMalloc(&s->d_tim, sizeof(float) * size);
-  if (e == cudaSuccess) e = cudaMalloc(&s->d_tim4, sizeof(float4) * (size_t)(size / 2));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_tim_ph, sizeof(float2) * (size_t)size);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_X, sizeof(float2) * nb);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_pspec, sizeof(float) * nb);
   if (e == cudaSuccess) e = cudaMalloc(&s->d_median, sizeof(float) * nb);
@@ -628,8 +632,8 @@ int ps_search_whiten(ps_search* hs, const unsigned char* d_trial, float* h_mean,
   if ((rc = launch_pass1<true>(p, lc, st))) return rc;
   StoreTransposedPairs so{reinterpret_cast<float2*>(s->d_tim), 0, 0, s->lg_n2, s->col_len};
   if ((rc = launch_pass2<true>(p, so, st))) return rc;
-  quad_pairs_kernel<<<ew_grid(p->M, 256, 4), 256, 0, st>>>(reinterpret_cast<const float2*>(s->d_tim), s->d_tim4, p->M, s->col_len);
-  PS_LAUNCHED("quad_pairs_kernel");
+  phase_planes_kernel<<<ew_grid(p->M, 256, 4), 256, 0, st>>>(reinterpret_cast<const float2*>(s->d_tim), s->d_tim_ph, p->M, s->col_len);
+  PS_LAUNCHED("phase_planes_kernel");
   if (h_mean || h_std) {
     float h[3];
     PS_CUDA(cudaMemcpyAsync(h, s->d_stats, sizeof(h), cudaMemcpyDeviceToHost, st), "Error from d2hcpy");
@@ -716,7 +720,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     last_nb = nb;
     LoadResampled ld;
     ld.D = reinterpret_cast<const float2*>(s->d_tim);
-    ld.D4 = s->d_tim4;
+    ld.Dph = s->d_tim_ph;
     ld.n1 = s->col_len;
     ld.lg_n2 = s->lg_n2;
     for (int b = 0; b < nb; b++) ld.afs.v[b] = accel_fact(h_acc[j + b], s->prm.tsamp);
@@ -828,21 +832,21 @@ int ps_search_resample_index_map(ps_search* hs, float acc, uint32_t* d_idx, unsi
   const ps_fft_plan_t* p = s->plan;
   const unsigned size = s->prm.size;
   float2* ramp = nullptr;
-  float4* ramp4 = nullptr;
+  float2* ramp_ph = nullptr;
   unsigned* d_cnt = nullptr;
   PS_CUDA(cudaMalloc(&ramp, sizeof(float) * (size_t)size), "Error from device_malloc");
-  if (cudaMalloc(&ramp4, sizeof(float4) * (size_t)(size / 2)) != cudaSuccess || cudaMalloc(&d_cnt, sizeof(unsigned)) != cudaSuccess) {
+  if (cudaMalloc(&ramp_ph, sizeof(float2) * (size_t)size) != cudaSuccess || cudaMalloc(&d_cnt, sizeof(unsigned)) != cudaSuccess) {
     cudaFree(ramp);
-    cudaFree(ramp4);
+    cudaFree(ramp_ph);
     return cuda_fail(cudaGetLastError(), "Error from device_malloc");
   }
   cudaMemsetAsync(d_cnt, 0, sizeof(unsigned), st);
   ramp_pairs_kernel<<<ew_grid(p->M, 256, 2), 256, 0, st>>>(ramp, p->M, s->col_len, s->lg_n2);
-  quad_pairs_kernel<<<ew_grid(p->M, 256, 4), 256, 0, st>>>(ramp, ramp4, p->M, s->col_len);  // as ps_search_whiten does
+  phase_planes_kernel<<<ew_grid(p->M, 256, 4), 256, 0, st>>>(ramp, ramp_ph, p->M, s->col_len);  // as ps_search_whiten does
   g_launches.fetch_add(2);
   LoadResampled ld;  // set up exactly as ps_search_accel_batch does for a one-trial batch
   ld.D = ramp;
-  ld.D4 = ramp4;
+  ld.Dph = ramp_ph;
   ld.n1 = s->col_len;
   ld.lg_n2 = s->lg_n2;
   ld.afs.v[0] = accel_fact(acc, s->prm.tsamp);
@@ -855,7 +859,7 @@ int ps_search_resample_index_map(ps_search* hs, float acc, uint32_t* d_idx, unsi
   cudaError_t e = cudaMemcpyAsync(&cnt, d_cnt, sizeof(unsigned), cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   cudaFree(ramp);
-  cudaFree(ramp4);
+  cudaFree(ramp_ph);
   cudaFree(d_cnt);
   if (e != cudaSuccess) return cuda_fail(e, "ps_search_resample_index_map");
   if (h_exact_pairs) *h_exact_pairs = cnt;

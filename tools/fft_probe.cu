@@ -148,10 +148,10 @@ int main() {
   run<5>("noC", Yt, sn, t, n1, n2, nbatch);
   {
     float* D; cudaMalloc(&D, sizeof(cf) * M); cudaMemset(D, 0, sizeof(cf) * M);
-    float4* D4; cudaMalloc(&D4, sizeof(float4) * M); cudaMemset(D4, 0, sizeof(float4) * M);  // two-phase form the loader reads
+    float2* Dph; cudaMalloc(&Dph, sizeof(float2) * 2 * M); cudaMemset(Dph, 0, sizeof(float2) * 2 * M);  // two-phase form the loader reads
     LoadResampled ld;
     ld.D = reinterpret_cast<const float2*>(D);
-    ld.D4 = D4;
+    ld.Dph = Dph;
     double af = ((30.0f * 64e-6f) / (2 * 299792458.0));
     for (int b = 0; b < 8; b++) ld.afs.v[b] = af * (b + 1) / 2;
     ld.size = 2.0 * M; ld.n1 = n1; ld.lg_n2 = 11;
