@@ -375,7 +375,9 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant
   const int dtile = (int)gridDim.x / nbatch, db = (int)gridDim.x - dtile * nbatch;
   int tile = work / nbatch, b = work - tile * nbatch;
   for (; work < nwork; work += gridDim.x) {
-    StorePass1<INV> st{Yt + (size_t)b * M, t, n1, tile * C::F, n2, tw2};
+    cf* Yb = Yt + (size_t)b * M;
+    asm volatile("" : "+l"(Yb));  // one pointer per item: keeps the 64-bit product b * M out of every store's address
+    StorePass1<INV> st{Yb, t, n1, tile * C::F, n2, tw2};
     C::phaseA_regs_w(threadIdx.x, smem, wA, v);
     __syncthreads();
     C::phaseB_w(threadIdx.x, smem, wB, st);
