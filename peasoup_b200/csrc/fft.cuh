@@ -256,14 +256,53 @@ struct StorePass1 {
   FftTables t;
   int n1, c0;
   int n2, tw;  // Yt is tiled for pass 2: Yt[k1 / tw][j2][k1 % tw], tw = rows per pass-2 tile
+  // W_M^(f u) of this thread (direction applied): depends on the thread only, so a kernel looks it up once
+  cf wfu = psfft::mk(1.f, 0.f);
+  bool wfu_set = false;
   // outputs k = k0 + stride*j of column j2: multiply by W_M^(j2*k) = base * step^j (two
   // interleaved chains, <= R/2 roundings deep) and store the column run
   template <int R>
   __device__ __forceinline__ void store(int f, int k0, int stride, const cf* v) const {
     const unsigned j2 = (unsigned)(c0 + f);
-    const cf base = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k0));
+    store_with<R>(f, k0, stride, v, psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)k0)),
+                  psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride)));
+  }
+
+  // Phase C hands over the outputs q_m = u + G m, m = 0, 1, ... of thread row u in sequence.  Looking
+  // W_M^(j2 q_m) up per call costs a scattered table read each (32 distinct entries per warp: ~30 L1
+  // wavefronts); instead W_M^(j2 u) = W_M^(c0 u) W_M^(f u) (8 distinct entries per warp and a
+  // thread constant), advanced by W_M^(j2 G) (4 distinct entries) from call to call, and the step
+  // W_M^(256 j2) is that factor's square when 256 = 2 G.  One or two extra roundings on the twiddle.
+  static constexpr bool kSequenced = true;
+  struct Seq {
+    cf cur, g, step;
+  };
+  template <int G>
+  __device__ __forceinline__ Seq seq_begin(int f, int u, int stride) const {
+    const unsigned j2 = (unsigned)(c0 + f);
+    Seq q;
+    const cf wf = wfu_set ? wfu : psfft::dirw<INV>(twiddle_M(t, (unsigned)f * (unsigned)u));
+    q.cur = psfft::cmul(psfft::dirw<INV>(twiddle_M(t, (unsigned)c0 * (unsigned)u)), wf);
+    q.g = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)G));
+    if (stride == G)
+      q.step = q.g;
+    else if (stride == 2 * G)
+      q.step = psfft::cmul(q.g, q.g);
+    else
+      q.step = psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride));
+    return q;
+  }
+  template <int R>
+  __device__ __forceinline__ void store_seq(int f, int k0, int stride, const cf* v, Seq& q) const {
+    store_with<R>(f, k0, stride, v, q.cur, q.step);
+    q.cur = psfft::cmul(q.cur, q.g);
+  }
+
+  template <int R>
+  __device__ __forceinline__ void store_with(int f, int k0, int stride, const cf* v, cf base, cf step1) const {
+    const unsigned j2 = (unsigned)(c0 + f);
     cf pw[R > 1 ? R : 2];
-    psfft::chain_powers<R>(pw, base, psfft::dirw<INV>(twiddle_M(t, j2 * (unsigned)stride)));
+    psfft::chain_powers<R>(pw, base, step1);
     // tw (rows per pass-2 tile, a power of two <= 32) divides the stride of every call but the 16-point one:
     // the run position k % tw is then the same for all j and the R stores are one base address plus
     // multiples of a constant -- 32-bit element offsets inside this item's slice (M <= 2^24 elements)
@@ -371,13 +410,14 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant
   ld.begin(work % nbatch, (work / nbatch) * C::F, n2);
   load_operands<C>(ld, v);
   const cf wA = C::twiddleA(threadIdx.x, t.W4096), wB = R3 > 1 ? C::twiddleB(threadIdx.x, t.W4096) : psfft::mk(1.f, 0.f);
+  const cf wfu = psfft::dirw<INV>(twiddle_M(t, (threadIdx.x % C::F) * (threadIdx.x / C::F)));  // StorePass1::wfu
   // (tile, b) of the work item whose operands are in v, stepped by the grid size without a division
   const int dtile = (int)gridDim.x / nbatch, db = (int)gridDim.x - dtile * nbatch;
   int tile = work / nbatch, b = work - tile * nbatch;
   for (; work < nwork; work += gridDim.x) {
     cf* Yb = Yt + (size_t)b * M;
     asm volatile("" : "+l"(Yb));  // one pointer per item: keeps the 64-bit product b * M out of every store's address
-    StorePass1<INV> st{Yb, t, n1, tile * C::F, n2, tw2};
+    StorePass1<INV> st{Yb, t, n1, tile * C::F, n2, tw2, wfu, true};
     C::phaseA_regs_w(threadIdx.x, smem, wA, v);
     __syncthreads();
     C::phaseB_w(threadIdx.x, smem, wB, st);

@@ -16,6 +16,7 @@
 #pragma once
 #include <stddef.h>
 #include <stdint.h>
+#include <type_traits>
 
 #if defined(__CUDACC__)
 #define PS_HD __host__ __device__ __forceinline__
@@ -168,6 +169,12 @@ PS_HD void chain_powers(cf* w, cf base, cf s1) {
   }
 }
 
+// storers with kSequenced = true take phase C's calls through seq_begin / store_seq
+template <class S, class = void>
+struct is_sequenced { static constexpr bool value = false; };
+template <class S>
+struct is_sequenced<S, typename std::enable_if<S::kSequenced>::type> { static constexpr bool value = true; };
+
 // One CTA-wide batch of F FFTs of length n = 256*R3.  512 threads; thread t = u*F + f.
 // Shared memory holds complex words (8 bytes): a warp always touches 32 consecutive complex
 // words (256 contiguous bytes, two conflict-free half-warp phases).
@@ -248,14 +255,28 @@ struct CtaFft {
     const int f = t % F, u = t / F;
     const cf* e2 = reinterpret_cast<const cf*>(s) + E1_WORDS;
     constexpr int RR = (R3 > 1) ? R3 : 2;
+    if constexpr (is_sequenced<Storer>::value) {
+      // the storer derives the per-call state of call m + 1 from call m's (fft.cuh: StorePass1::store_seq)
+      auto sq = st.template seq_begin<G>(f, u, 256);
 #pragma unroll
-    for (int m = 0; m < 16 / RR; m++) {
-      const int q = u + G * m;
-      cf w[RR];
+      for (int m = 0; m < 16 / RR; m++) {
+        const int q = u + G * m;
+        cf w[RR];
 #pragma unroll
-      for (int c = 0; c < RR; c++) w[c] = e2[(q * (R3 + 1) + c) * F + f];
-      dftR<RR, INV>(w);
-      st.template store<RR>(f, q, 256, w);
+        for (int c = 0; c < RR; c++) w[c] = e2[(q * (R3 + 1) + c) * F + f];
+        dftR<RR, INV>(w);
+        st.template store_seq<RR>(f, q, 256, w, sq);
+      }
+    } else {
+#pragma unroll
+      for (int m = 0; m < 16 / RR; m++) {
+        const int q = u + G * m;
+        cf w[RR];
+#pragma unroll
+        for (int c = 0; c < RR; c++) w[c] = e2[(q * (R3 + 1) + c) * F + f];
+        dftR<RR, INV>(w);
+        st.template store<RR>(f, q, 256, w);
+      }
     }
   }
 };
