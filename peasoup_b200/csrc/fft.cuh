@@ -422,6 +422,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant
     __syncthreads();
     C::phaseB_w(threadIdx.x, smem, wB, st);
     // (issued before the barrier: the loads are in flight while the CTA waits for its slowest warp)
+    auto sq = st.template seq_begin<C::G>(threadIdx.x % C::F, threadIdx.x / C::F, 256);
     tile += dtile;
     b += db;
     if (b >= nbatch) {
@@ -433,7 +434,7 @@ __global__ void __launch_bounds__(512, 1) fft_pass1_kernel(const __grid_constant
       load_operands<C>(ld, v);
     }
     __syncthreads();
-    C::phaseC(threadIdx.x, smem, st);
+    C::phaseC_seq(threadIdx.x, smem, st, sq);
   }
 }
 

@@ -249,6 +249,25 @@ struct CtaFft {
     for (int kb = 0; kb < 16; kb++) e2[((ka + 16 * kb) * (R3 + 1) + c) * F + f] = v[kb];
   }
 
+  // phase C of a sequenced storer whose state was begun earlier (its table reads then fly during the
+  // barrier in front of phase C): sq = st.seq_begin<G>(t % F, t / F, 256)
+  template <class Storer, class Seq>
+  PS_HD static void phaseC_seq(int t, const float* s, const Storer& st, Seq& sq) {
+    if (R3 == 1) return;
+    const int f = t % F, u = t / F;
+    const cf* e2 = reinterpret_cast<const cf*>(s) + E1_WORDS;
+    constexpr int RR = (R3 > 1) ? R3 : 2;
+#pragma unroll
+    for (int m = 0; m < 16 / RR; m++) {
+      const int q = u + G * m;
+      cf w[RR];
+#pragma unroll
+      for (int c = 0; c < RR; c++) w[c] = e2[(q * (R3 + 1) + c) * F + f];
+      dftR<RR, INV>(w);
+      st.template store_seq<RR>(f, q, 256, w, sq);
+    }
+  }
+
   template <class Storer>
   PS_HD static void phaseC(int t, const float* s, const Storer& st) {
     if (R3 == 1) return;
@@ -258,15 +277,7 @@ struct CtaFft {
     if constexpr (is_sequenced<Storer>::value) {
       // the storer derives the per-call state of call m + 1 from call m's (fft.cuh: StorePass1::store_seq)
       auto sq = st.template seq_begin<G>(f, u, 256);
-#pragma unroll
-      for (int m = 0; m < 16 / RR; m++) {
-        const int q = u + G * m;
-        cf w[RR];
-#pragma unroll
-        for (int c = 0; c < RR; c++) w[c] = e2[(q * (R3 + 1) + c) * F + f];
-        dftR<RR, INV>(w);
-        st.template store_seq<RR>(f, q, 256, w, sq);
-      }
+      phaseC_seq(t, s, st, sq);
     } else {
 #pragma unroll
       for (int m = 0; m < 16 / RR; m++) {
