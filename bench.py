@@ -392,7 +392,7 @@ def run_config3(args):
                    "d2h_bytes_per_step": int(4 + 16 * npk)},
            "gpu_launches": int(launches), "clocks": clocks, "peaks_per_step": npk,
            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
-                        "peak_source": peak_src, "kernel": "harmonic_peaks_smem_kernel<4>",
+                        "peak_source": peak_src, "kernel": "harmonic_peaks_rows_kernel<4>",
                         "algorithmic_bytes_per_launch": int(4 * nb * n), "ms_per_launch": 1e3 * t,
                         "note": "the stage pulls 8.5 words per bin out of the L2 (the operand ranges of the 15 fractions): "
                                 "L2 -> SM traffic, not HBM, bounds it"}}

@@ -186,7 +186,7 @@ int ps_search_reserve_peaks(ps_search* s, unsigned max_peaks);
  * spectrum b reported as acceleration index acc_idx0 + b.  Peaks join the handle's peak list
  * (ps_search_reset_peaks / ps_search_fetch_peaks).  Spectra that are 16-byte aligned, a multiple of
  * 4 floats apart and followed by >= 4 readable floats each are summed from TMA-staged operands
- * (harmonic_smem.cuh); any other layout takes the gather kernel.  Same output either way.
+ * (harmonic_rows.cuh); any other layout takes the gather kernel.  Same output either way.
  * Also BASELINE.json configs[2]'s microbench. */
 int ps_search_harmonic_peaks(ps_search* s, const float* d_spectra, size_t stride, int nbatch,
                              int acc_idx0, void* stream);

@@ -203,8 +203,59 @@ __device__ __noinline__ void hp_emit_slow(const float* __restrict__ P, int nbins
   }
 }
 
+// The same for lanes that own sixteen CONSECUTIVE bins (harmonic_rows.cuh): bit i of a lane's mask = bin
+// warp_base + 16 lane + i.  A cluster of neighbouring bins sits in one lane there, so the flagged bins of the
+// warp are first spread over its lanes (sixteen ballots, the n-th flagged bin goes to lane n % 32): one
+// round of the exact re-evaluation per 32 flagged bins, however they are distributed.
+__device__ __noinline__ void hp_emit_rows(const float* __restrict__ P, int nbins, int warp_base, int lane, unsigned mask, int nh,
+                                          int nfolds, const LevelRanges& r, float thresh, int acc_idx, const PeakSink& sink) {
+  unsigned bal[16];
+  int total = 0;
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    bal[i] = __ballot_sync(0xffffffffu, (mask >> i) & 1u);
+    total += __popc(bal[i]);
+  }
+#pragma unroll 1
+  for (int n0 = 0; n0 < total; n0 += 32) {
+    const int n = n0 + lane;
+    int idx = -1;
+    if (n < total) {
+      int c = 0;
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        const int pc = __popc(bal[i]);
+        if (idx < 0 && n < c + pc) idx = warp_base + 16 * (int)__fns(bal[i], 0, n - c + 1) + i;
+        c += pc;
+      }
+    }
+    bool hit = false;
+    float v = 0.f;
+    if (idx >= 0 && idx < nbins) {
+      float f[5];
+      harmonic_folds(P, idx, nfolds, f);
+      v = nh == 0 ? __ldg(P + idx) : f[nh - 1];
+      hit = idx >= r.start[nh] && idx < r.limit[nh] && v > thresh;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (m) {
+      unsigned pos = 0;
+      if (lane == 0) pos = atomicAdd(sink.count, (unsigned)__popc(m));
+      pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1));
+      if (hit && pos < sink.cap) {
+        ps_raw_peak pk;
+        pk.acc_idx = acc_idx;
+        pk.nh = nh;
+        pk.bin = idx;
+        pk.snr = v;
+        sink.peaks[pos] = pk;
+      }
+    }
+  }
+}
+
 }  // namespace ps
-#include "harmonic_smem.cuh"
+#include "harmonic_rows.cuh"
 namespace ps {
 
 template <int NF, bool FULL>
@@ -494,21 +545,35 @@ struct ps_search {
 };
 static Search* SS(ps_search* s) { return reinterpret_cast<Search*>(s); }
 
-// harmonic sums + peaks with TMA-staged operands (harmonic_smem.cuh); spectra must be padded
-template <int NF>
-static int launch_harmonic_smem_nf(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
-  auto k = harmonic_peaks_smem_kernel<NF>;
+// harmonic sums + peaks with TMA-staged operands (harmonic_rows.cuh); spectra must be 16-byte aligned and padded
+template <int NF, int W = kHrW, int CTAS = kHrCtas>
+static int launch_harmonic_rows_nf(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
+  auto k = harmonic_peaks_rows_kernel<NF, W, CTAS>;
   static SmemOptIn done[64];
-  const size_t smem = sizeof(float) * hs_total(NF) * kHsBufs;
+  const size_t smem = sizeof(float) * hr_total<W>(NF);
   int rc = configure_smem(k, smem, s->plan->device, done);
   if (rc) return rc;
   PeakSink sink{s->d_peaks, s->d_count, s->cap};
-  const int ntiles = ((int)s->nbins + kHsW - 1) / kHsW;
-  const int work = ntiles * nb, cap = 148 * kHsCtas;
-  k<<<work < cap ? work : cap, kHsThreads, smem, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, acc_idx0,
-                                                      sink, ntiles, nb);
-  PS_LAUNCHED("harmonic_peaks_smem_kernel");
+#ifdef PS_PROFILING
+  {
+    const int probe = getenv("PS_HS_PROBE") ? atoi(getenv("PS_HS_PROBE")) : 0;
+    cudaMemcpyToSymbolAsync(g_hs_probe, &probe, sizeof(int), 0, cudaMemcpyHostToDevice, st);
+  }
+#endif
+  const int ntiles = ((int)s->nbins + W - 1) / W;
+  const int work = ntiles * nb, cap = 148 * CTAS;
+  k<<<work < cap ? work : cap, W / 16, smem, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, acc_idx0,
+                                                   sink, ntiles, nb);
+  PS_LAUNCHED("harmonic_peaks_rows_kernel");
   return PS_OK;
+}
+
+static int launch_harmonic_staged(Search* s, const float* sp, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
+  const int nf = s->prm.nharmonics;
+  return nf == 1 ? launch_harmonic_rows_nf<1>(s, sp, stride, nb, acc_idx0, st)
+       : nf == 2 ? launch_harmonic_rows_nf<2>(s, sp, stride, nb, acc_idx0, st)
+       : nf == 3 ? launch_harmonic_rows_nf<3>(s, sp, stride, nb, acc_idx0, st)
+                 : launch_harmonic_rows_nf<4>(s, sp, stride, nb, acc_idx0, st);
 }
 
 extern "C" {
@@ -688,10 +753,7 @@ int ps_search_harmonic_peaks(ps_search* hs, const float* d_spectra, size_t strid
     int nb = std::min(32768, nbatch - j);
     const float* sp = d_spectra + (size_t)j * stride;
     int rc = !staged ? launch_harmonic_peaks(s, sp, stride, nb, acc_idx0 + j, S(stream))
-             : nf == 1 ? launch_harmonic_smem_nf<1>(s, sp, stride, nb, acc_idx0 + j, S(stream))
-             : nf == 2 ? launch_harmonic_smem_nf<2>(s, sp, stride, nb, acc_idx0 + j, S(stream))
-             : nf == 3 ? launch_harmonic_smem_nf<3>(s, sp, stride, nb, acc_idx0 + j, S(stream))
-                       : launch_harmonic_smem_nf<4>(s, sp, stride, nb, acc_idx0 + j, S(stream));
+                     : launch_harmonic_staged(s, sp, stride, nb, acc_idx0 + j, S(stream));
     if (rc) return rc;
   }
   return PS_OK;
@@ -740,12 +802,8 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
     if (env_skip & 8) continue;
     static const int env_hsmem = getenv("PS_HSMEM") ? atoi(getenv("PS_HSMEM")) : 1;
     const int nf = s->prm.nharmonics;
-    if (env_hsmem && nf >= 1 && nf <= 4) {  // the pipeline's own spectra are padded: TMA-staged variant
-      rc = nf == 1 ? launch_harmonic_smem_nf<1>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st)
-         : nf == 2 ? launch_harmonic_smem_nf<2>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st)
-         : nf == 3 ? launch_harmonic_smem_nf<3>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st)
-                   : launch_harmonic_smem_nf<4>(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st);
-      if (rc) return rc;
+    if (env_hsmem && nf >= 1 && nf <= 4) {  // the pipeline's own spectra are padded: TMA-staged variants
+      if ((rc = launch_harmonic_staged(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st))) return rc;
       continue;
     }
     if ((rc = launch_harmonic_peaks(s, s->d_pbatch, s->pstride, nb, acc_idx0 + j, st))) return rc;
