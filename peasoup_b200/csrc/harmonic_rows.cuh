@@ -109,11 +109,14 @@ __device__ __forceinline__ void hr_add(float* acc, const float* __restrict__ q, 
 template <int NF, int W = kHrW, int CTAS = kHrCtas>
 __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const float* __restrict__ Pall, int nbins, size_t pstride,
                                                                             LevelRanges r, LevelScales ls, float thresh, int acc_idx0,
-                                                                            PeakSink sink, int ntiles, int nbatch) {
+                                                                            PeakSink sink, int ntiles, int nbatch,
+                                                                            unsigned long long* __restrict__ dispenser,
+                                                                            unsigned long long dispenser_base) {
   static_assert(NF >= 1 && NF <= 4, "shared-memory staging is sized for up to 4 folds");
   constexpr int NFR = hs_nfrac(NF);
   extern __shared__ __align__(128) float sm[];
   __shared__ __align__(8) unsigned long long bar;
+  __shared__ int s_next[2];
   const int lane = threadIdx.x & 31;
   const int j = threadIdx.x;  // lane of the tile: bins k0 + 16 j + i
   const int nwork = ntiles * nbatch;
@@ -128,9 +131,17 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
     fence_proxy_async();
   }
   __syncthreads();
+  // Tiles are handed out dynamically: tiles with peaks cost microseconds more (hp_emit_rows) and a static
+  // partition left 8 % of the SM time idle behind the slowest CTA.  A CTA starts with tile blockIdx.x and
+  // draws the next one from a counter that only grows (this launch's numbers start at dispenser_base;
+  // nwork >= gridDim.x, so a launch draws nwork numbers in all: nwork - gridDim.x tiles and one miss per CTA).
+  // Thread 0 draws while the current tile is summed; the result crosses the end-of-tile barrier in shared memory.
   unsigned parity = 0;
-  for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
-    const bool staged_item = probe != 1 || work == (int)blockIdx.x;
+  int it = 0;
+  for (int work = blockIdx.x; work < nwork; it++) {
+    unsigned long long drawn = 0;
+    if (threadIdx.x == 0) drawn = atomicAdd(dispenser, 1ULL);
+    const bool staged_item = probe != 1 || it == 0;
     const int b = work / ntiles, tile = work - b * ntiles;
     const float* __restrict__ P = Pall + (size_t)b * pstride;
     const int k0 = tile * W;
@@ -205,7 +216,9 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
   }
     PS_HS_FRACTIONS(PS_HR_ADD)
 #undef PS_HR_ADD
+    if (threadIdx.x == 0) s_next[it & 1] = (int)(drawn - dispenser_base) + (int)gridDim.x;
     __syncthreads();  // all warps are done with the buffer: the next iteration's copies may overwrite it
+    work = s_next[it & 1];
   }
 }
 

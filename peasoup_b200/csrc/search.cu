@@ -502,6 +502,9 @@ struct Search {
   unsigned nbirdies = 0;
   ps_raw_peak* d_peaks = nullptr;
   unsigned* d_count = nullptr;
+  // tile dispenser of harmonic_peaks_rows_kernel: a counter that only grows; a launch starts at hwork_base
+  unsigned long long* d_hwork = nullptr;
+  unsigned long long hwork_base = 0;
   unsigned cap = 0;
   unsigned needed = 0;  // record count of the last fetch (ps_search_peaks_needed)
   LevelRanges ranges;
@@ -519,7 +522,7 @@ static void free_search(Search* s) {
   plan_destroy(s->plan);
   cudaFree(s->d_tim); cudaFree(s->d_tim_nat); cudaFree(s->d_tim_ph); cudaFree(s->d_X); cudaFree(s->d_pspec); cudaFree(s->d_median); cudaFree(s->d_work);
   cudaFree(s->d_stats); cudaFree(s->d_partials); cudaFree(s->d_u8sum); cudaFree(s->d_birdies); cudaFree(s->d_widths);
-  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_pbatch);
+  cudaFree(s->d_peaks); cudaFree(s->d_count); cudaFree(s->d_hwork); cudaFree(s->d_pbatch);
   delete s;
 }
 
@@ -563,7 +566,8 @@ static int launch_harmonic_rows_nf(Search* s, const float* d_spectra, size_t str
   const int ntiles = ((int)s->nbins + W - 1) / W;
   const int work = ntiles * nb, cap = 148 * CTAS;
   k<<<work < cap ? work : cap, W / 16, smem, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, acc_idx0,
-                                                   sink, ntiles, nb);
+                                                   sink, ntiles, nb, s->d_hwork, s->hwork_base);
+  s->hwork_base += (unsigned long long)work;  // the launch draws exactly `work` numbers (harmonic_rows.cuh)
   PS_LAUNCHED("harmonic_peaks_rows_kernel");
   return PS_OK;
 }
@@ -629,6 +633,8 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (e == cudaSuccess) e = cudaMalloc(&s->d_count, sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMalloc(&s->d_pbatch, sizeof(float) * s->pstride * s->batch);
   if (e == cudaSuccess) e = cudaMemset(s->d_count, 0, sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_hwork, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(s->d_hwork, 0, sizeof(unsigned long long));
   if (e != cudaSuccess) {
     free_search(s);
     return cuda_fail(e, "Error from device_malloc");
