@@ -73,7 +73,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // Every loader/storer has begin(b, first, n): b = batch item (independent transform sharing the
 // plan), first = first column (pass 1) / row (pass 2) of the CTA tile, n = n2 (pass 1) / n1 (pass 2).
 // complex element e = idx*n2 + c0 + f of the packed series
-constexpr int kMaxBatch = 64;
+constexpr int kMaxBatch = 128;
 
 struct LoadPackedReal {  // z[e] = (x[2e], x[2e+1])
   static constexpr bool kAsync = true;

@@ -24,8 +24,8 @@ int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
 // us/trial at 2^23 -- r1: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7; r2: 26: 49.7, 34: 49.5, 51: 49.1).  Up to 64,
 // fewer for long transforms: the inter-pass buffer, the packed spectra and the spectra of a launch
 // (20 bytes per sample and trial) are kept under kBatchBytes per handle.
-constexpr int kAccelBatch = 64;
-constexpr size_t kBatchBytes = (size_t)12 << 30;
+constexpr int kAccelBatch = 128;
+constexpr size_t kBatchBytes = (size_t)24 << 30;
 static int accel_batch_for(unsigned size) {
   const size_t per_trial = (size_t)20 * size;
   return (int)std::max<size_t>(8, std::min<size_t>(kAccelBatch, kBatchBytes / per_trial));
