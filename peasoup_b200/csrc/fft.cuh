@@ -113,6 +113,11 @@ struct LoadResampled {
   // exactly 2c + parity and the rest is the row, so either pair is ONE aligned 8-byte load behind a
   // mask, a shift and a multiply-add -- no second address, no divergence on the parity -- and the 8
   // rows x 4 columns a warp reads (nearly always of one parity) are 4 runs of 64 bytes.
+  // (Measured against it: the same two planes in natural order, Dph[parity * M + (i0 >> 1)] -- at 2^24 and
+  // +-500 m/s^2, where the shift changes by 3.6 samples from one row of a column to the next and every
+  // operand of a transposed column lies in a plane column of its own: 111.1 against 107.9 us / trial, and
+  // 100.1 against 92.6 at small accelerations; 45.5 against 45.1 at 2^23.  What costs at large
+  // accelerations is the width of the band the trials of a launch read, see ps_search_accel_batch.)
   const float2* D;
   const float2* Dph;
   AccelFacts afs;
@@ -541,14 +546,14 @@ inline int configure_smem(K kernel, size_t bytes, int device, SmemOptIn* done) {
 inline int fft_grid(int ntiles) { return ntiles < 148 ? ntiles : 148; }
 
 template <int R3, bool INV, class Loader>
-inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch) {
+inline int launch_pass1_r(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch, int batch0) {
   using C = psfft::CtaFft<R3, INV>;
   auto k = fft_pass1_kernel<R3, INV, Loader>;
   static SmemOptIn done[64];
   const size_t smem = C::SMEM_BYTES;
   int rc = configure_smem(k, smem, p->device, done);
   if (rc) return rc;
-  k<<<fft_grid(p->n2 / C::F * nbatch), C::THREADS, smem, st>>>(ld, p->Yt, p->tables(), p->n1, p->n2, nbatch, 32 / p->r2);
+  k<<<fft_grid(p->n2 / C::F * nbatch), C::THREADS, smem, st>>>(ld, p->Yt + (size_t)batch0 * p->M, p->tables(), p->n1, p->n2, nbatch, 32 / p->r2);
   PS_LAUNCHED("fft_pass1_kernel");
   return PS_OK;
 }
@@ -577,8 +582,9 @@ inline int launch_pass2_r(const ps_fft_plan_t* p, const Storer& stor, cudaStream
   }
 
 template <bool INV, class Loader>
-inline int launch_pass1(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch = 1) {
-#define PS_CALL1(R) launch_pass1_r<R, INV, Loader>(p, ld, st, nbatch)
+// nbatch transforms into the inter-pass slices batch0 .. batch0 + nbatch - 1
+inline int launch_pass1(const ps_fft_plan_t* p, const Loader& ld, cudaStream_t st, int nbatch = 1, int batch0 = 0) {
+#define PS_CALL1(R) launch_pass1_r<R, INV, Loader>(p, ld, st, nbatch, batch0)
   PS_DISPATCH_R(p->r1, PS_CALL1)
 #undef PS_CALL1
 }

@@ -580,6 +580,23 @@ static int launch_harmonic_staged(Search* s, const float* sp, size_t stride, int
                  : launch_harmonic_rows_nf<4>(s, sp, stride, nb, acc_idx0, st);
 }
 
+// loader of one launch: the acceleration factors of its nb trials and the bounds the float32 estimate needs
+static void setup_resampler(LoadResampled& ld, const Search* s, const float2* pairs, const float2* planes, const float* h_acc, int nb) {
+  const double size = (double)s->prm.size;
+  ld.D = pairs;
+  ld.Dph = planes;
+  ld.n1 = s->col_len;
+  ld.lg_n2 = s->lg_n2;
+  double amax = 0;
+  for (int b = 0; b < nb; b++) {
+    ld.afs.v[b] = accel_fact(h_acc[b], s->prm.tsamp);
+    amax = std::max(amax, fabs(ld.afs.v[b]));
+  }
+  ld.size = size;
+  ld.max_shift = (float)(amax * 0.25 * size * size * 1.001);  // |i(i-N)| <= N^2/4
+  ld.max_step = (float)(amax * size * 1.001);                 // |d/di| <= N
+}
+
 extern "C" {
 
 int ps_search_create(const ps_search_params* p, ps_search** out) {
@@ -780,26 +797,39 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
   constexpr int env_skip = 0;
 #endif
   static const int env_rev = getenv("PS_REVERSE") ? atoi(getenv("PS_REVERSE")) : 1;
+  static const double band_bytes = (getenv("PS_BAND_MB") ? atof(getenv("PS_BAND_MB")) : 24.0) * 1048576.0;
   // balanced launches: 101 trials at up to 16 per launch run as 15+15+15+14+14+14+14, not 6x16+5
   int launches_left = (n_acc + env_batch - 1) / env_batch;
   int last_nb = 1;
   for (int j = 0, nb = 0; j < n_acc; j += nb, launches_left--) {
     nb = (n_acc - j + launches_left - 1) / launches_left;
     last_nb = nb;
-    LoadResampled ld;
-    ld.D = reinterpret_cast<const float2*>(s->d_tim);
-    ld.Dph = s->d_tim_ph;
-    ld.n1 = s->col_len;
-    ld.lg_n2 = s->lg_n2;
-    for (int b = 0; b < nb; b++) ld.afs.v[b] = accel_fact(h_acc[j + b], s->prm.tsamp);
-    ld.size = (double)size;
-    {
-      double amax = 0;
-      for (int b = 0; b < nb; b++) amax = std::max(amax, fabs(ld.afs.v[b]));
-      ld.max_shift = (float)(amax * 0.25 * (double)size * (double)size * 1.001);  // |i(i-N)| <= N^2/4
-      ld.max_step = (float)(amax * (double)size * 1.001);                         // |d/di| <= N
+    if (!(env_skip & 1)) {
+      // Pass 1 of the launch's nb trials in groups of neighbouring accelerations: the trials of a group are
+      // transformed tile by tile together, and at any time they read a band of the series as wide as the
+      // difference of their shifts (up to (af_hi - af_lo) N^2 / 8 pairs = plane columns of n1 pairs).  The
+      // band has to stay in the L2 from one tile to the next: at 2^24 and +-500 m/s^2 a 67-trial launch
+      // spans 1250 columns = 80 MB and 41 % of the loads went to DRAM; groups are cut at PS_BAND_MB (24 MB:
+      // chain us / trial for 201 trials at 6 / 10 / 14 / 20 / 40 / 60 MB and uncut: 106.4 / 104.2 / 103.5 / 102.0 / 103.0 / 106.8 / 109.6).
+      const float2* pairs = reinterpret_cast<const float2*>(s->d_tim);
+      const double col_bytes = 16.0 * (double)s->col_len, quarter = 0.125 * (double)size * (double)size;
+      for (int g0 = 0; g0 < nb;) {
+        double lo = accel_fact(h_acc[j + g0], s->prm.tsamp), hi = lo;
+        int g1 = g0 + 1;
+        for (; g1 < nb; g1++) {
+          const double a = accel_fact(h_acc[j + g1], s->prm.tsamp);
+          const double nlo = std::min(lo, a), nhi = std::max(hi, a);
+          if ((nhi - nlo) * quarter * col_bytes > band_bytes) break;
+          lo = nlo;
+          hi = nhi;
+        }
+        LoadResampled ld;
+        setup_resampler(ld, s, pairs, s->d_tim_ph, h_acc + j + g0, g1 - g0);
+        rc = launch_pass1<false>(p, ld, st, g1 - g0, g0);
+        if (rc) return rc;
+        g0 = g1;
+      }
     }
-    if (!(env_skip & 1) && (rc = launch_pass1<false>(p, ld, st, nb))) return rc;
     {
       StoreNatural sn{reinterpret_cast<float2*>(p->Z), (size_t)p->M, 0, 0, nullptr};
       if (!(env_skip & 2) && (rc = launch_pass2<false>(p, sn, st, nb, env_rev))) return rc;
@@ -907,16 +937,9 @@ int ps_search_resample_index_map(ps_search* hs, float acc, uint32_t* d_idx, unsi
   cudaMemsetAsync(d_cnt, 0, sizeof(unsigned), st);
   ramp_pairs_kernel<<<ew_grid(p->M, 256, 2), 256, 0, st>>>(ramp, p->M, s->col_len, s->lg_n2);
   phase_planes_kernel<<<ew_grid(p->M, 256, 4), 256, 0, st>>>(ramp, ramp_ph, p->M, s->col_len);  // as ps_search_whiten does
-  g_launches.fetch_add(2);
+  g_launches.fetch_add(1);
   LoadResampled ld;  // set up exactly as ps_search_accel_batch does for a one-trial batch
-  ld.D = ramp;
-  ld.Dph = ramp_ph;
-  ld.n1 = s->col_len;
-  ld.lg_n2 = s->lg_n2;
-  ld.afs.v[0] = accel_fact(acc, s->prm.tsamp);
-  ld.size = (double)size;
-  ld.max_shift = (float)(fabs(ld.afs.v[0]) * 0.25 * (double)size * (double)size * 1.001);
-  ld.max_step = (float)(fabs(ld.afs.v[0]) * (double)size * 1.001);
+  setup_resampler(ld, s, ramp, ramp_ph, &acc, 1);
   loader_dump_kernel<<<ew_grid(p->M, 256, 2), 256, 0, st>>>(ld, reinterpret_cast<float2*>(d_idx), p->M, p->n2, d_cnt);
   g_launches.fetch_add(1);
   unsigned cnt = 0;
