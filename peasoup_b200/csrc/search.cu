@@ -21,7 +21,8 @@ namespace ps {
 
 int plan_create(unsigned n, ps_fft_plan_t** out, int max_batch);
 // acceleration trials per launch: amortises kernel ramp-up/drain and the 148-SM wave tail (measured chain
-// us/trial at 2^23 -- r1: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7; r2: 26: 49.7, 34: 49.5, 51: 49.1).  Up to 64,
+// us/trial at 2^23 -- r1: 1: 94, 2: 74, 4: 65, 8: 61, 16: 59, 32: 57.7; r2: 26: 49.7, 34: 49.5, 51: 49.1; 34: 46.1, 51: 45.8,
+// 101: 45.0).  Up to 128,
 // fewer for long transforms: the inter-pass buffer, the packed spectra and the spectra of a launch
 // (20 bytes per sample and trial) are kept under kBatchBytes per handle.
 constexpr int kAccelBatch = 128;
@@ -608,6 +609,7 @@ int ps_search_create(const ps_search_params* p, ps_search** out) {
   if (s->prm.boundary_5_freq <= 0) s->prm.boundary_5_freq = 0.05f;
   if (s->prm.boundary_25_freq <= 0) s->prm.boundary_25_freq = 0.5f;
   s->batch = accel_batch_for(p->size);
+  if (const char* e = getenv("PS_BATCH")) s->batch = std::max(1, std::min(s->batch, atoi(e)));  // (also bounds the handle's memory: 20 bytes per sample and trial)
   int rc = plan_create(p->size, &s->plan, s->batch);
   if (rc) {
     delete s;
@@ -798,7 +800,7 @@ int ps_search_accel_batch(ps_search* hs, const float* h_acc, int n_acc, int acc_
 #endif
   static const int env_rev = getenv("PS_REVERSE") ? atoi(getenv("PS_REVERSE")) : 1;
   static const double band_bytes = (getenv("PS_BAND_MB") ? atof(getenv("PS_BAND_MB")) : 24.0) * 1048576.0;
-  // balanced launches: 101 trials at up to 16 per launch run as 15+15+15+14+14+14+14, not 6x16+5
+  // balanced launches: 201 trials at up to 71 per launch run as 67+67+67, not 71+71+59
   int launches_left = (n_acc + env_batch - 1) / env_batch;
   int last_nb = 1;
   for (int j = 0, nb = 0; j < n_acc; j += nb, launches_left--) {
