@@ -469,3 +469,37 @@ def test_product_resample_index_map_bit_exact(lib, oracle, size):
         worst = max(worst, exact / (size / 2))
     assert worst < 0.03, (size, worst)   # float32 estimate decides > 97 % of the pairs even at 2^25 / 500 m/s^2
     s.close()
+
+
+_BAND_SCRIPT = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, {repo!r}); sys.path.insert(0, {tests!r})
+import peasoup_b200 as pb
+from peasoup_b200.host import make_search_params
+from synth import make_trials
+size, tsamp = 1 << 19, 64e-6
+trial = make_trials(1, size, size, tsamp=tsamp, a_inj=31.4, amp=10.0)[0]
+s = pb.Search(make_search_params(size, size, tsamp, min_snr=6.0))
+s.whiten(torch.from_numpy(trial).cuda())
+accs = np.array([0.0, 31.4, -12.0, 400.0, 401.0, -350.0, 5.0], np.float32)
+s.reset_peaks(); s.accel_batch(accs)
+np.save(sys.argv[1], s.fetch_peaks())
+"""
+
+
+def test_pass1_acceleration_groups_equal_one_group(lib, tmp_path):
+    """ps_search_accel_batch runs pass 1 of a launch in groups of neighbouring accelerations (PS_BAND_MB of
+    shift band per group, each group into its own slices of the inter-pass buffer).  With a band of a few
+    bytes every trial is a group of its own, with a huge one the launch is one group: same raw peaks."""
+    import subprocess
+    import sys
+    script = tmp_path / "band.py"
+    script.write_text(_BAND_SCRIPT.format(repo=pb.REPO, tests=os.path.join(pb.REPO, "tests")))
+    out = {}
+    for name, mb in (("split", "0.000001"), ("whole", "1000000")):
+        env = dict(os.environ, PS_BAND_MB=mb)
+        path = tmp_path / f"{name}.npy"
+        subprocess.run([sys.executable, str(script), str(path)], check=True, env=env, timeout=300)
+        out[name] = np.load(path)
+    assert len(out["split"]) > 100
+    assert out["split"].tobytes() == out["whole"].tobytes()
