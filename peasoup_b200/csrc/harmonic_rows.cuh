@@ -69,6 +69,23 @@ __host__ __device__ constexpr int hr_offset(int f) { return f == 0 ? 0 : hr_offs
 template <int W>
 __host__ __device__ constexpr int hr_total(int nf) { return hs_nfrac(nf) == 0 ? 4 : hr_offset<W>(hs_nfrac(nf) - 1) + hr_words<W>(hs_nfrac(nf) - 1); }
 
+// the last word any lane reads of fraction f's range -- lane W/16 - 1, operand max c, rounded up to the
+// vector load that fetches it -- lies inside the words reserved (and copied) for that range
+template <int W>
+__host__ __device__ constexpr bool hr_reads_fit() {
+  for (int f = 0; f < 15; f++) {
+    const int m16 = hr_m16(f), nw = hr_cmax(m16) + 1;
+    const int vec = m16 % 2 == 1 ? 1 : m16 % 4 == 2 ? 2 : 4;
+    const int last = (W / 16 - 1) * m16 + ((nw + vec - 1) / vec) * vec - 1;
+    // (a remainder word behind full vectors is a single 4-byte load of word nw - 1)
+    const int last_exact = (W / 16 - 1) * m16 + nw - 1;
+    if ((nw % vec == 0 ? last : last_exact) >= hr_words<W>(f)) return false;
+  }
+  return true;
+}
+static_assert(hr_reads_fit<kHrW>(), "a lane would read past its staged range");
+static_assert(sizeof(float) * hr_total<kHrW>(4) * kHrCtas <= 227 * 1024 - 1024 * kHrCtas, "kHrCtas tiles of staging do not fit a SM");
+
 // acc[i] += staged[j M16 + c_i]; q = the lane's first word (range base + j M16)
 template <int M16>
 __device__ __forceinline__ void hr_add(float* acc, const float* __restrict__ q, int lane) {

@@ -568,8 +568,8 @@ static int launch_harmonic_rows_nf(Search* s, const float* d_spectra, size_t str
   const int work = ntiles * nb, cap = 148 * CTAS;
   k<<<work < cap ? work : cap, W / 16, smem, st>>>(d_spectra, (int)s->nbins, stride, s->ranges, s->scales, s->prm.min_snr, acc_idx0,
                                                    sink, ntiles, nb, s->d_hwork, s->hwork_base);
-  s->hwork_base += (unsigned long long)work;  // the launch draws exactly `work` numbers (harmonic_rows.cuh)
   PS_LAUNCHED("harmonic_peaks_rows_kernel");
+  s->hwork_base += (unsigned long long)work;  // a launch that was accepted draws exactly `work` numbers (harmonic_rows.cuh)
   return PS_OK;
 }
 
