@@ -5,9 +5,13 @@
 // CONTIGUOUS input range [p(k0), p(k0+W-1)], p(k) = (k m + 2^(s-1)) >> s: fifteen ranges (1/2; 1/4,
 // 3/4; odd/8; odd/16) of 7.5 W words in total.  Fifteen threads issue one cp.async.bulk copy each
 // (completion on an mbarrier): the L2 sees fifteen streaming reads per tile instead of 15 scattered
-// 4-byte loads per bin, and the gathers read shared memory.  Seven 64-thread CTAs (1024-bin tiles,
-// 30.8 KB of staging each) per SM take turns copying and summing (chain us / trial for tiles of
+// 4-byte loads per bin, and the gathers read shared memory.  Eight 64-thread CTAs (1024-bin tiles,
+// 26.3 KB of staging each) per SM take turns copying and summing (chain us / trial for tiles of
 // 512 / 1024 / 2048 bins with 14 / 7 / 3 CTAs per SM: 51.7 / 45.9 / 47.1; six CTAs of 1024: 46.1).
+// The five smallest fractions -- 1/2, 1/4, 1/8, 1/16 and 3/16, 1.1 of the 7.5 words per bin -- are not
+// staged: a lane reads their 2..9 consecutive words from global memory together with its own bins
+// (23 registers), which is what lets the eighth CTA fit (chain 45.0 -> 44.6 us / trial; the same with
+// seven CTAs: 45.0).
 //
 // With bins k0 + 16 j + i (i < 16) in lane j of a tile that starts at a multiple of 1024, the read
 // index of the fraction m / 2^s is  p = P0 + j M16 + c_i,  P0 = k0 m >> s (a multiple of 4),
@@ -57,17 +61,22 @@ __device__ int g_hs_probe;  // 1: no staging copies after a CTA's first tile, 2:
 
 constexpr int kHrW = 1024;            // bins per tile
 constexpr int kHrThreads = kHrW / 16;  // 64
-constexpr int kHrCtas = 7;            // CTAs per SM (30.8 KB of staging each)
+constexpr int kHrCtas = 8;            // CTAs per SM (26.3 KB of staging each)
 
 __host__ __device__ constexpr int hr_m16(int f) { return hs_m(f) << (4 - hs_s(f)); }
 __host__ __device__ constexpr int hr_cmax(int m16) { return (15 * m16 + 8) >> 4; }
-// words reserved for fraction f: W M16 / 16 + 1, rounded up to a multiple of 4 (16-byte copies and 16-byte aligned regions)
-template <int W>
-__host__ __device__ constexpr int hr_words(int f) { return (((W * hr_m16(f)) >> 4) + 1 + 3) & ~3; }
-template <int W>
-__host__ __device__ constexpr int hr_offset(int f) { return f == 0 ? 0 : hr_offset<W>(f - 1) + hr_words<W>(f - 1); }
-template <int W>
-__host__ __device__ constexpr int hr_total(int nf) { return hs_nfrac(nf) == 0 ? 4 : hr_offset<W>(hs_nfrac(nf) - 1) + hr_words<W>(hs_nfrac(nf) - 1); }
+// words reserved for fraction f: W M16 / 16 + 1, rounded up to a multiple of 4 (16-byte copies and 16-byte aligned regions);
+// fractions in DMASK are not staged (their few words per lane come straight from global memory)
+template <int W, int DMASK = 0>
+__host__ __device__ constexpr int hr_words(int f) { return ((DMASK >> f) & 1) ? 0 : (((W * hr_m16(f)) >> 4) + 1 + 3) & ~3; }
+template <int W, int DMASK = 0>
+__host__ __device__ constexpr int hr_offset(int f) { return f == 0 ? 0 : hr_offset<W, DMASK>(f - 1) + hr_words<W, DMASK>(f - 1); }
+template <int W, int DMASK = 0>
+__host__ __device__ constexpr int hr_total(int nf) {
+  return hs_nfrac(nf) == 0 ? 4 : hr_offset<W, DMASK>(hs_nfrac(nf) - 1) + hr_words<W, DMASK>(hs_nfrac(nf) - 1) + 4;
+}
+// fractions 1/2, 1/4, 1/8, 1/16, 3/16 (indices 0, 2, 3, 7, 8 of the accumulation order): M16 = 8, 4, 2, 1, 3
+constexpr int kHrDirect = (1 << 0) | (1 << 2) | (1 << 3) | (1 << 7) | (1 << 8);
 
 // the last word any lane reads of fraction f's range -- lane W/16 - 1, operand max c, rounded up to the
 // vector load that fetches it -- lies inside the words reserved (and copied) for that range
@@ -84,13 +93,13 @@ __host__ __device__ constexpr bool hr_reads_fit() {
   return true;
 }
 static_assert(hr_reads_fit<kHrW>(), "a lane would read past its staged range");
-static_assert(sizeof(float) * hr_total<kHrW>(4) * kHrCtas <= 227 * 1024 - 1024 * kHrCtas, "kHrCtas tiles of staging do not fit a SM");
+static_assert((sizeof(float) * hr_total<kHrW, kHrDirect>(4) + 1152 + 1024) * kHrCtas <= 228 * 1024, "kHrCtas tiles of staging do not fit a SM");
 
-// acc[i] += staged[j M16 + c_i]; q = the lane's first word (range base + j M16)
+// the words of fraction M16 a lane needs: w[c] = q[c], q = the lane's first word (range base + j M16), in
+// shared memory (staged ranges) or global memory (direct fractions)
 template <int M16>
-__device__ __forceinline__ void hr_add(float* acc, const float* __restrict__ q, int lane) {
+__device__ __forceinline__ void hr_load(float* w, const float* __restrict__ q, int lane) {
   constexpr int NW = hr_cmax(M16) + 1;
-  float w[NW];
   if constexpr (M16 % 2 == 1) {
 #pragma unroll
     for (int c = 0; c < NW; c++) w[c] = q[c];
@@ -119,11 +128,21 @@ __device__ __forceinline__ void hr_add(float* acc, const float* __restrict__ q, 
       w[NW - 1] = last;
     }
   }
+}
+// acc[i] += w[c_i]
+template <int M16>
+__device__ __forceinline__ void hr_accum(float* acc, const float* w) {
 #pragma unroll
   for (int i = 0; i < 16; i++) acc[i] += w[(i * M16 + 8) >> 4];
 }
+template <int M16>
+__device__ __forceinline__ void hr_add(float* acc, const float* __restrict__ q, int lane) {
+  float w[hr_cmax(M16) + 1];
+  hr_load<M16>(w, q, lane);
+  hr_accum<M16>(acc, w);
+}
 
-template <int NF, int W = kHrW, int CTAS = kHrCtas>
+template <int NF, int W = kHrW, int CTAS = kHrCtas, int DMASK = kHrDirect>
 __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const float* __restrict__ Pall, int nbins, size_t pstride,
                                                                             LevelRanges r, LevelScales ls, float thresh, int acc_idx0,
                                                                             PeakSink sink, int ntiles, int nbatch,
@@ -131,6 +150,9 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
                                                                             unsigned long long dispenser_base) {
   static_assert(NF >= 1 && NF <= 4, "shared-memory staging is sized for up to 4 folds");
   constexpr int NFR = hs_nfrac(NF);
+  // staged fractions (one fold: the only fraction, 1/2, is read directly and nothing is staged)
+  constexpr int NSTAGED = NFR - ((DMASK & 1) + ((DMASK >> 2) & 1 & (NFR > 2)) + ((DMASK >> 3) & 1 & (NFR > 3)) +
+                                 ((DMASK >> 7) & 1 & (NFR > 7)) + ((DMASK >> 8) & 1 & (NFR > 8)));
   extern __shared__ __align__(128) float sm[];
   __shared__ __align__(8) unsigned long long bar;
   __shared__ int s_next[2];
@@ -144,7 +166,7 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
 #endif
 
   if (threadIdx.x == 0) {
-    mbar_init(&bar, NFR);
+    mbar_init(&bar, NSTAGED > 0 ? NSTAGED : 1);
     fence_proxy_async();
   }
   __syncthreads();
@@ -162,16 +184,16 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
     const int b = work / ntiles, tile = work - b * ntiles;
     const float* __restrict__ P = Pall + (size_t)b * pstride;
     const int k0 = tile * W;
-    if ((int)threadIdx.x < NFR && staged_item) {  // thread f stages the range of fraction f
+    if (NSTAGED > 0 && (int)threadIdx.x < NFR && !((DMASK >> threadIdx.x) & 1) && staged_item) {  // thread f stages the range of fraction f
       // (offset, length and first word from compile-time constants: no table read in front of the copy)
       const int f = threadIdx.x;
       int off = 0, m16 = 0, words = 0;
 #pragma unroll
       for (int g = 0; g < NFR; g++) {
-        if (g < f) off += hr_words<W>(g);
+        if (g < f) off += hr_words<W, DMASK>(g);
         if (g == f) {
           m16 = hr_m16(g);
-          words = hr_words<W>(g);
+          words = hr_words<W, DMASK>(g);
         }
       }
       const int first = (k0 >> 4) * m16;  // = hs_p(k0, m, s), a multiple of 4: k0 is a multiple of 512
@@ -200,6 +222,16 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
 #pragma unroll
       for (int i = 0; i < 16; i++) acc[i] = base + i < nbins ? __ldg(P + base + i) : 0.f;
     }
+    // the direct fractions' words, requested with the own bins (in flight while the ranges are staged)
+    float wd0[9], wd2[5], wd3[3], wd7[2], wd8[4];
+    {
+      const float* __restrict__ Pg = P + (k0 >> 4);  // P0 = (k0 / 16) M16
+      if ((DMASK >> 0) & 1 && 0 < NFR) hr_load<8>(wd0, Pg + (size_t)(k0 >> 4) * 7 + j * 8, lane);
+      if ((DMASK >> 2) & 1 && 2 < NFR) hr_load<4>(wd2, Pg + (size_t)(k0 >> 4) * 3 + j * 4, lane);
+      if ((DMASK >> 3) & 1 && 3 < NFR) hr_load<2>(wd3, Pg + (size_t)(k0 >> 4) * 1 + j * 2, lane);
+      if ((DMASK >> 7) & 1 && 7 < NFR) hr_load<1>(wd7, Pg + j, lane);
+      if ((DMASK >> 8) & 1 && 8 < NFR) hr_load<3>(wd8, Pg + (size_t)(k0 >> 4) * 2 + j * 3, lane);
+    }
     auto emit = [&](int nh) {
       float mx = acc[0];
 #pragma unroll
@@ -216,7 +248,7 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
       hp_emit_rows(P, nbins, base - 16 * lane, lane, mask, nh, NF, r, thresh, acc_idx0 + b, sink);
     };
     emit(0);
-    if (staged_item) {
+    if (NSTAGED > 0 && staged_item) {
       mbar_wait(&bar, parity);
       parity ^= 1u;
     }
@@ -224,7 +256,10 @@ __global__ void __launch_bounds__(W / 16, CTAS) harmonic_peaks_rows_kernel(const
   if ((I) < NFR) {                                                           \
     if (probe != 2) {                                                        \
       constexpr int m16_ = (M_) << (4 - (S_));                               \
-      hr_add<m16_>(acc, sm + hr_offset<W>(I) + j * m16_, lane);                 \
+      if ((DMASK >> (I)) & 1)                                                \
+        hr_accum<m16_>(acc, (I) == 0 ? wd0 : (I) == 2 ? wd2 : (I) == 3 ? wd3 : (I) == 7 ? wd7 : wd8); \
+      else                                                                   \
+        hr_add<m16_>(acc, sm + hr_offset<W, DMASK>(I) + j * m16_, lane);     \
     }                                                                        \
     if ((I) == 0) emit(1);                                                   \
     if ((I) == 2) emit(2);                                                   \

@@ -550,11 +550,11 @@ struct ps_search {
 static Search* SS(ps_search* s) { return reinterpret_cast<Search*>(s); }
 
 // harmonic sums + peaks with TMA-staged operands (harmonic_rows.cuh); spectra must be 16-byte aligned and padded
-template <int NF, int W = kHrW, int CTAS = kHrCtas>
+template <int NF, int W = kHrW, int CTAS = kHrCtas, int DMASK = kHrDirect>
 static int launch_harmonic_rows_nf(Search* s, const float* d_spectra, size_t stride, int nb, int acc_idx0, cudaStream_t st) {
-  auto k = harmonic_peaks_rows_kernel<NF, W, CTAS>;
+  auto k = harmonic_peaks_rows_kernel<NF, W, CTAS, DMASK>;
   static SmemOptIn done[64];
-  const size_t smem = sizeof(float) * hr_total<W>(NF);
+  const size_t smem = sizeof(float) * hr_total<W, DMASK>(NF);
   int rc = configure_smem(k, smem, s->plan->device, done);
   if (rc) return rc;
   PeakSink sink{s->d_peaks, s->d_count, s->cap};
