@@ -12,4 +12,4 @@ dump() {  # name, mangled function
 dump fft_pass1 _ZN2ps16fft_pass1_kernelILi8ELb0ENS_13LoadResampledEEEvT1_PN5psfft2cfENS_9FftTablesEiiii
 dump fft_pass2 _ZN2ps16fft_pass2_kernelILi8ELb0ENS_12StoreNaturalEEEvPKN5psfft2cfET1_NS_9FftTablesEiiii
 dump spectrum _ZN2ps15spectrum_kernelEPK6float2PfjmPKffPKN5psfft2cfES9_S0_
-dump harmonic_peaks_rows _ZN2ps26harmonic_peaks_rows_kernelILi4ELi1024ELi7EEEvPKfimNS_11LevelRangesENS_11LevelScalesEfiNS_8PeakSinkEiiPyy
+dump harmonic_peaks_rows _ZN2ps26harmonic_peaks_rows_kernelILi4ELi1024ELi8ELi397EEEvPKfimNS_11LevelRangesENS_11LevelScalesEfiNS_8PeakSinkEiiPyy
