@@ -1,3 +1,5 @@
+"""Chain time per acceleration trial at 2^24 samples against the acceleration range of the list (profiles/r02_summary.md
+r2l): the band of the series the trials of a launch read grows with the range; PS_BAND_MB cuts pass 1 into groups."""
 import sys, os
 sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
 import numpy as np, torch
