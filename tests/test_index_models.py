@@ -71,3 +71,39 @@ def test_pass1_store_base_plus_step_is_the_tiled_index():
                         assert want.max() < 2 ** 32
                     else:
                         assert r3 == 1 and tw == 32  # the 16-point stage with 32-row tiles keeps the general form
+
+
+def test_flagged_bins_are_spread_over_the_warp_once_each():
+    """hp_emit_rows (search.cu): bit i of lane l's mask = bin 16 l + i; the flagged bins of a warp are enumerated as
+    sixteen ballots, word i first; the n-th goes to lane n % 32 of round n / 32 (found with popc + fns).  Every
+    flagged bin must be evaluated exactly once."""
+    rng = np.random.default_rng(11)
+
+    def fns(word, k):  # position of the k-th (1-based) set bit of a 32-bit word, as __fns(word, 0, k)
+        for pos in range(32):
+            if (word >> pos) & 1:
+                k -= 1
+                if k == 0:
+                    return pos
+        return -1
+
+    for density in (0.0, 0.01, 0.2, 0.9, 1.0):
+        masks = [int(sum((1 << i) for i in range(16) if rng.random() < density)) for _ in range(32)]
+        flagged = {16 * l + i for l in range(32) for i in range(16) if (masks[l] >> i) & 1}
+        bal = [sum((((masks[l] >> i) & 1) << l) for l in range(32)) for i in range(16)]
+        total = sum(bin(b).count("1") for b in bal)
+        assert total == len(flagged)
+        seen = []
+        for n0 in range(0, total, 32):
+            for lane in range(32):
+                n = n0 + lane
+                if n >= total:
+                    continue
+                c, idx = 0, -1
+                for i in range(16):
+                    pc = bin(bal[i]).count("1")
+                    if idx < 0 and n < c + pc:
+                        idx = 16 * fns(bal[i], n - c + 1) + i
+                    c += pc
+                seen.append(idx)
+        assert sorted(seen) == sorted(flagged)
